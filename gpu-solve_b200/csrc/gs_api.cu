@@ -1,0 +1,1197 @@
+// gs_api.cu — the C ABI of include/gpusolve_cuda.h: level hierarchy and device
+// memory, V-cycle / solve / Newton orchestration (host control that the reference
+// keeps in CpuSolver::solve/vcycle and NewtonSolver::solve/findError), CUDA-graph
+// capture of the V-cycle, field I/O, config parsing.  All numerical work happens
+// in the kernels of kernels_simple.cu / kernels_fast.cu; there is no CPU
+// arithmetic path here beyond sqrt() of the reduced norm and level constants.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "gs_comm.h"
+#include "gs_internal.h"
+
+// ---------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(expr)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e__ = (expr);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return fail(GS_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+#define GS(expr)                  \
+    do {                          \
+        int rc__ = (expr);        \
+        if (rc__ != GS_OK) return rc__; \
+    } while (0)
+
+// ---------------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------------
+struct Level {
+    Geom g;
+    double h;
+    PointK k;
+    bool pow2;
+    int zlo, zhi;     // owned GLOBAL planes [zlo, zhi) (both physical halo planes belong to the end ranks)
+    int ib, ie;       // LOCAL plane range [ib, ie) of owned interior planes
+    bool replicated;  // whole level held (and computed) by every rank
+    size_t count;     // doubles per array
+    double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
+    bool coef_valid;
+};
+
+struct EventPair {
+    cudaEvent_t a, b;
+    int op, level;
+};
+
+struct gs_handle {
+    gs_params p;
+    int device, rank, world;
+    std::vector<Level> lev;
+    StencilOff so;
+    bool canonical;
+    double* newtonF;
+    bool newton_begun;
+    cudaStream_t stream;
+    LaunchCtx cx;
+    double* h_norm;  // pinned
+    uint64_t launches;
+    int opt_kernels, opt_graph, opt_timing;
+    std::map<uint64_t, cudaGraphExec_t> graphs;
+    std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
+    std::vector<double> history;
+    std::vector<EventPair> ev_used;
+    std::vector<cudaEvent_t> ev_free;
+    double op_ms[GS_OP_COUNT];
+    uint64_t op_launches[GS_OP_COUNT];
+    std::vector<double> lvl_ms;          // [level][op]
+    std::vector<uint64_t> lvl_launches;  // [level][op]
+    GsComm* comm;
+    int replicated_from;
+};
+
+namespace {
+
+struct OpScope {  // CUDA-event bracket around one operator when "timing" is on
+    gs_handle* h;
+    int op, level;
+    cudaEvent_t a, b;
+    uint64_t l0;
+    OpScope(gs_handle* h_, int op_, int level_) : h(h_), op(op_), level(level_), a(nullptr), b(nullptr), l0(h_->launches)
+    {
+        if (!h->opt_timing) return;
+        a = get();
+        b = get();
+        cudaEventRecord(a, h->stream);
+    }
+    ~OpScope()
+    {
+        h->op_launches[op] += h->launches - l0;
+        h->lvl_launches[(size_t)level * GS_OP_COUNT + op] += h->launches - l0;
+        if (!h->opt_timing) return;
+        cudaEventRecord(b, h->stream);
+        h->ev_used.push_back({a, b, op, level});
+    }
+    cudaEvent_t get()
+    {
+        cudaEvent_t e;
+        if (!h->ev_free.empty()) {
+            e = h->ev_free.back();
+            h->ev_free.pop_back();
+        } else {
+            cudaEventCreate(&e);
+        }
+        return e;
+    }
+};
+
+int num_levels_for(const gs_params& p)
+{
+    // src/cpu/CpuGridData.cpp:19
+    uint64_t m = std::min(std::min(p.dim[0], p.dim[1]), p.dim[2]);
+    return (int)floor(log((double)m) / log(2.0)) + 1;
+}
+
+void level_dims(const gs_params& p, int level, uint64_t n[3])
+{
+    // src/cpu/CpuGridData.cpp:23-29: integer halving per axis
+    for (int d = 0; d < 3; d++) n[d] = p.dim[d];
+    for (int l = 0; l < level; l++)
+        for (int d = 0; d < 3; d++) n[d] /= 2;
+}
+
+bool is_pow2(double x)
+{
+    int e;
+    return x > 0 && std::isfinite(x) && frexp(x, &e) == 0.5;
+}
+
+int validate(const gs_params& p)
+{
+    if (p.mode < 0 || p.mode > 2) return fail(GS_EINVAL, "Invalid mode %d", p.mode);
+    for (int d = 0; d < 3; d++)
+        if (p.dim[d] < 1 || p.dim[d] > 4000) return fail(GS_EINVAL, "grid dimension %d out of range: %llu", d, (unsigned long long)p.dim[d]);
+    for (int i = 0; i < 7; i++)
+        for (int d = 0; d < 3; d++)
+            if (p.stencil_off[i][d] < -1 || p.stencil_off[i][d] > 1)
+                return fail(GS_EINVAL, "stencil offset [%d][%d]=%d outside {-1,0,1} (halo width is 1)", i, d, p.stencil_off[i][d]);
+    if (p.stencil_val[0] == 0.0) return fail(GS_EINVAL, "stencil centre value (first entry) must be non-zero");
+    return GS_OK;
+}
+
+bool canonical_offsets(const gs_params& p)
+{
+    static const int c[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+    for (int i = 0; i < 7; i++)
+        for (int d = 0; d < 3; d++)
+            if (p.stencil_off[i][d] != c[i][d]) return false;
+    return true;
+}
+
+// slab boundaries: see gs_partition
+struct Partition {
+    int nlev;
+    int replicated_from;              // first level held whole by every rank
+    std::vector<std::vector<int>> b;  // b[level][rank] .. b[level][world]
+};
+
+Partition make_partition(const gs_params& p, int world)
+{
+    Partition P;
+    P.nlev = num_levels_for(p);
+    P.b.resize(P.nlev);
+    int min_planes = 4;
+    if (const char* e = getenv("GPUSOLVE_SLAB_MIN")) min_planes = std::max(1, atoi(e));
+    // deepest level that still gives every rank >= min_planes planes; never the last two levels
+    int deepest = -1;
+    if (world > 1) {
+        for (int l = 0; l + 2 < P.nlev; l++) {
+            uint64_t n[3];
+            level_dims(p, l, n);
+            int Zm1 = (int)n[2] + 1;
+            int blk = (Zm1 + world - 1) / world;
+            if (blk >= min_planes && (world - 1) * blk < Zm1) deepest = l;
+            else break;
+        }
+    }
+    P.replicated_from = deepest + 1;
+    for (int l = 0; l < P.nlev; l++) {
+        uint64_t n[3];
+        level_dims(p, l, n);
+        const int Z = (int)n[2] + 2;
+        P.b[l].assign(world + 1, 0);
+        if (l >= P.replicated_from) {
+            for (int r = 0; r <= world; r++) P.b[l][r] = r == 0 ? 0 : Z;  // everyone holds [0, Z)
+            continue;
+        }
+        uint64_t nd[3];
+        level_dims(p, deepest, nd);
+        const int blk_deep = ((int)nd[2] + 1 + world - 1) / world;
+        for (int r = 0; r < world; r++) P.b[l][r] = std::min(Z, (r * blk_deep) << (deepest - l));
+        P.b[l][world] = Z;
+    }
+    return P;
+}
+
+int alloc_zero(double** p, size_t count)
+{
+    cudaError_t e = cudaMalloc((void**)p, count * sizeof(double));
+    if (e != cudaSuccess) return fail(GS_ENOMEM, "cudaMalloc of %zu bytes failed: %s", count * sizeof(double), cudaGetErrorString(e));
+    CU(cudaMemset(*p, 0, count * sizeof(double)));
+    return GS_OK;
+}
+
+double** field_ptr(gs_handle* h, int level, int field)
+{
+    if (field == GS_FIELD_NEWTONF) return level == 0 ? &h->newtonF : nullptr;
+    if (level < 0 || level >= (int)h->lev.size()) return nullptr;
+    Level& L = h->lev[level];
+    switch (field) {
+    case GS_FIELD_V: return &L.v;
+    case GS_FIELD_F: return &L.f;
+    case GS_FIELD_R: return &L.r;
+    case GS_FIELD_RESTV: return &L.restV;
+    case GS_FIELD_NEWTONV: return &L.newtonV;
+    }
+    return nullptr;
+}
+
+int check_level(const gs_handle* h, int level)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    if (level < 0 || level >= (int)h->lev.size()) return fail(GS_EINVAL, "level %d out of range [0,%d)", level, (int)h->lev.size());
+    return GS_OK;
+}
+
+int smoother_km(const gs_handle* h)
+{
+    switch (h->p.mode) {
+    case GS_MODE_LINEAR: return KM_LINEAR;
+    case GS_MODE_NONLINEAR: return KM_NONLINEAR;
+    default: return h->opt_kernels ? KM_NEWTON_COEF : KM_NEWTON_EXP;
+    }
+}
+
+bool partitioned(const gs_handle* h, int level) { return h->world > 1 && !h->lev[level].replicated; }
+
+// ---- multi-GPU helpers (no-ops on one GPU) ----------------------------------------
+// refresh `depth` ghost planes on both sides of a partitioned level array
+int exchange_halo(gs_handle* h, int level, double* a, int depth)
+{
+    if (!partitioned(h, level)) return GS_OK;
+    Level& L = h->lev[level];
+    const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;  // local owned range
+    int rc = gs_comm_halo(h->comm, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, h->stream);
+    if (rc != 0) return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
+    return GS_OK;
+}
+
+// ---- operators ------------------------------------------------------------------
+int ensure_coef(gs_handle* h, int level)
+{
+    Level& L = h->lev[level];
+    if (L.coef_valid) return GS_OK;
+    OpScope t(h, GS_OP_OTHER, level);
+    CU(ks_newton_coef(h->cx, L.g, 0, L.g.nzl, h->p.gamma, L.newtonV, L.coef));
+    L.coef_valid = true;
+    return GS_OK;
+}
+
+const double* smoother_aux(gs_handle* h, int level, int km)
+{
+    Level& L = h->lev[level];
+    if (km == KM_NEWTON_EXP) return L.newtonV;
+    if (km == KM_NEWTON_COEF) return L.coef;
+    return nullptr;
+}
+
+// CpuSolver::jacobi (src/cpu/CpuSolver.cpp:141-179) as fused ping-pong sweeps
+int do_smooth(gs_handle* h, int level, uint64_t iters)
+{
+    Level& L = h->lev[level];
+    const int km = smoother_km(h);
+    if (km == KM_NEWTON_COEF && iters > 0) GS(ensure_coef(h, level));
+    OpScope t(h, GS_OP_SMOOTH, level);
+    for (uint64_t it = 0; it < iters; it++) {
+        bool handled = false;
+        if (h->opt_kernels && h->canonical)
+            CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, smoother_aux(h, level, km), &handled));
+        if (!handled)
+            CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, smoother_aux(h, level, km)));
+        std::swap(L.v, L.vtmp);
+        GS(exchange_halo(h, level, L.v, 1));
+    }
+    return GS_OK;
+}
+
+// sum over ranks of the device scalar, copy to the pinned host slot (async)
+int norm_to_host(gs_handle* h, int level)
+{
+    if (partitioned(h, level)) {
+        if (gs_comm_allreduce_sum(h->comm, h->cx.norm.result, 1, h->stream) != 0)
+            return fail(GS_ECOMM, "norm all-reduce failed: %s", gs_comm_error(h->comm));
+    }
+    CU(cudaMemcpyAsync(h->h_norm, h->cx.norm.result, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return GS_OK;
+}
+
+// CpuSolver::compResidual (src/cpu/CpuSolver.cpp:45-83); the square root is taken by the caller
+int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
+{
+    Level& L = h->lev[level];
+    int km = smoother_km(h);
+    if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
+    OpScope t(h, GS_OP_RESIDUAL, level);
+    CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
+    return GS_OK;
+}
+
+// restrict a level array onto the next level (src/cpu/CpuSolver.cpp:211-238);
+// on the first replicated level the slabs are gathered so every rank holds it whole
+int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, double* coarse2)
+{
+    Level& F = h->lev[level];
+    Level& C = h->lev[level + 1];
+    int zb = C.ib, ze = C.ie;
+    if (partitioned(h, level) && C.replicated) {
+        // this rank computes the coarse planes whose centre fine plane it owns
+        zb = std::max(1, (F.zlo + 1) / 2);
+        ze = std::min(C.g.nz + 1, (F.zhi + 1) / 2);
+    }
+    CU(ks_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2));
+    if (partitioned(h, level) && C.replicated) {
+        for (double* a : {coarse, coarse2}) {
+            if (!a) continue;
+            if (gs_comm_gather_planes(h->comm, a, C.g.plane, level, h->stream) != 0)
+                return fail(GS_ECOMM, "coarse gather failed: %s", gs_comm_error(h->comm));
+        }
+    } else {
+        GS(exchange_halo(h, level + 1, coarse, 1));
+        if (coarse2) GS(exchange_halo(h, level + 1, coarse2, 1));
+    }
+    return GS_OK;
+}
+
+// compResidual(level) ; restrict(r -> f_{level+1})     src/cpu/CpuSolver.cpp:93-98
+int do_restrict_residual(gs_handle* h, int level)
+{
+    Level& L = h->lev[level];
+    OpScope t(h, GS_OP_RESTRICT, level);
+    int zb = L.ib, ze = L.ie;
+    if (partitioned(h, level)) {
+        // the lowest owned coarse plane needs r one fine plane below the slab, which needs v two below
+        GS(exchange_halo(h, level, L.v, 2));
+        if (L.zlo > 0) zb = L.ib - 1;
+    }
+    int km = smoother_km(h);
+    if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
+    CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
+    GS(do_restrict(h, level, L.r, h->lev[level + 1].f, nullptr));
+    return GS_OK;
+}
+
+// FAS coarse right-hand side, src/cpu/CpuSolver.cpp:106-112
+int do_fas_coarse_rhs(gs_handle* h, int level)
+{
+    Level& C = h->lev[level + 1];
+    OpScope t(h, GS_OP_RESTRICT, level);
+    GS(do_restrict(h, level, h->lev[level].v, C.restV, C.v));
+    CU(ks_fas_rhs(h->cx, C.pow2, C.g, C.ib, C.ie, C.k, h->so, C.restV, C.f, C.r));
+    return GS_OK;
+}
+
+// (mode 1: v_{l+1} -= restV_{l+1};) e = P v_{l+1}; v_l += e   src/cpu/CpuSolver.cpp:121-132
+int do_prolong_correct(gs_handle* h, int level)
+{
+    Level& F = h->lev[level];
+    Level& C = h->lev[level + 1];
+    OpScope t(h, GS_OP_PROLONG, level);
+    if (h->p.mode == GS_MODE_NONLINEAR) {
+        CU(ks_axpy(h->cx, C.g, 0, C.g.nzl, C.v, C.restV, -1));
+    }
+    // an odd number of sweeps per cycle would leave v/vtmp swapped; writing the corrected
+    // field out of place in that case keeps the buffer parity (and the CUDA graph) fixed
+    const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
+    CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
+    if (flip) std::swap(F.v, F.vtmp);
+    GS(exchange_halo(h, level, F.v, 1));
+    return GS_OK;
+}
+
+int zero_field(gs_handle* h, Level& L, double* a)
+{
+    OpScope t(h, GS_OP_OTHER, (int)(&L - h->lev.data()));
+    CU(cudaMemsetAsync(a, 0, L.count * sizeof(double), h->stream));
+    return GS_OK;
+}
+
+// everything CpuSolver::vcycle (src/cpu/CpuSolver.cpp:85-139) does, queued on the stream
+int enqueue_vcycle(gs_handle* h)
+{
+    const int last = (int)h->lev.size() - 1;
+    for (int i = 0; i < last; i++) {
+        GS(do_smooth(h, i, h->p.pre));
+        GS(do_restrict_residual(h, i));
+        if (h->p.mode != GS_MODE_NONLINEAR) GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));
+        else GS(do_fas_coarse_rhs(h, i));
+    }
+    GS(do_smooth(h, last, h->p.pre + h->p.post));
+    if ((h->p.pre + h->p.post) & 1) {  // restore buffer parity on the (tiny) coarsest level
+        Level& L = h->lev[last];
+        CU(cudaMemcpyAsync(L.vtmp, L.v, L.count * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        std::swap(L.v, L.vtmp);
+    }
+    for (int i = last; i > 0; i--) {
+        GS(do_prolong_correct(h, i - 1));
+        GS(do_smooth(h, i - 1, h->p.post));
+    }
+    GS(do_residual(h, 0, false, h->lev[0].ib, h->lev[0].ie));
+    GS(norm_to_host(h, 0));
+    return GS_OK;
+}
+
+uint64_t parity_key(const gs_handle* h)
+{
+    // which of the two buffers is `v` on each level, plus everything else a captured graph bakes in
+    uint64_t key = 0;
+    for (size_t l = 0; l < h->lev.size(); l++)
+        if (h->lev[l].v > h->lev[l].vtmp) key |= 1ull << l;
+    key |= (uint64_t)h->opt_kernels << 40;
+    key |= (uint64_t)(h->cx.tune.smooth_variant & 0x3f) << 32;
+    key ^= (uint64_t)(h->cx.tune.zchunk & 0xfff) << 20;
+    key |= (uint64_t)(h->p.pre & 0xff) << 44;
+    key |= (uint64_t)(h->p.post & 0xff) << 52;
+    return key;
+}
+
+int run_vcycle(gs_handle* h, double* norm)
+{
+    const bool need_coef = smoother_km(h) == KM_NEWTON_COEF;
+    if (need_coef)
+        for (size_t l = 0; l < h->lev.size(); l++) GS(ensure_coef(h, (int)l));
+    const bool graph_ok = h->opt_graph && !h->opt_timing && h->world == 1;
+    if (!graph_ok) {
+        GS(enqueue_vcycle(h));
+    } else {
+        const uint64_t key = parity_key(h);
+        auto it = h->graphs.find(key);
+        if (it == h->graphs.end()) {
+            std::vector<double*> v0, t0;
+            for (auto& L : h->lev) {
+                v0.push_back(L.v);
+                t0.push_back(L.vtmp);
+            }
+            const uint64_t l0 = h->launches;
+            cudaGraph_t g = nullptr;
+            CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+            int rc = enqueue_vcycle(h);
+            cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+            // capture ran the host-side pointer swaps once; undo them, the launch below redoes them
+            for (size_t l = 0; l < h->lev.size(); l++) {
+                h->lev[l].v = v0[l];
+                h->lev[l].vtmp = t0[l];
+            }
+            uint64_t per_cycle = h->launches - l0;
+            h->launches = l0;
+            if (rc != GS_OK) {
+                if (g) cudaGraphDestroy(g);
+                return rc;
+            }
+            CU(ce);
+            cudaGraphExec_t ex = nullptr;
+            CU(cudaGraphInstantiate(&ex, g, 0));
+            cudaGraphDestroy(g);
+            it = h->graphs.emplace(key, ex).first;
+            h->graphs_launches[key] = per_cycle;
+        }
+        CU(cudaGraphLaunch(it->second, h->stream));
+        h->launches += h->graphs_launches[key];
+        // host-side view of the buffer parity after the cycle
+        const int last = (int)h->lev.size() - 1;
+        const bool odd = ((h->p.pre + h->p.post) & 1) != 0;
+        (void)last;
+        (void)odd;  // parity is restored by construction (do_prolong_correct / coarsest copy)
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    *norm = sqrt(*h->h_norm);
+    return GS_OK;
+}
+
+// the early-exit test exactly as spelled in src/cpu/CpuSolver.cpp:39 / src/cpu/NewtonSolver.cpp:37
+bool reached(double res, double initial, double tol) { return res <= initial / (1.0 / tol); }
+
+long long ms_since(std::chrono::high_resolution_clock::time_point t0)
+{
+    return std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - t0).count();
+}
+
+int residual_norm_sync(gs_handle* h, int level, bool store_r, double* norm)
+{
+    Level& L = h->lev[level];
+    GS(do_residual(h, level, store_r, L.ib, L.ie));
+    GS(norm_to_host(h, level));
+    CU(cudaStreamSynchronize(h->stream));
+    *norm = sqrt(*h->h_norm);
+    return GS_OK;
+}
+
+// CpuSolver::solve, src/cpu/CpuSolver.cpp:12-43
+int solve_mg(gs_handle* h, uint64_t maxiter, double tol, bool print, std::vector<double>* hist, uint64_t* cycles,
+             bool* converged)
+{
+    double initial;
+    GS(residual_norm_sync(h, 0, true, &initial));
+    if (print) std::cout << "Inital residual: " << initial << '\n';
+    if (hist) hist->push_back(initial);
+    *cycles = 0;
+    *converged = false;
+    for (uint64_t i = 0; i < maxiter; i++) {
+        auto t0 = std::chrono::high_resolution_clock::now();
+        double res;
+        GS(run_vcycle(h, &res));
+        ++*cycles;
+        if (hist) hist->push_back(res);
+        if (print) {
+            std::cout << "iter: " << i << " residual: " << res << ' ';
+            std::cout << "Took " << ms_since(t0) << "ms\n";  // src/Timer.cpp:13-27
+        }
+        if (reached(res, initial, tol)) {
+            *converged = true;
+            break;
+        }
+    }
+    return GS_OK;
+}
+
+int newton_begin(gs_handle* h)
+{
+    // NewtonSolver::solve line 12: newtonF = level0.f, "never gets changed"
+    Level& L = h->lev[0];
+    CU(cudaMemcpyAsync(h->newtonF, L.f, L.count * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    h->newton_begun = true;
+    return GS_OK;
+}
+
+// NewtonSolver::compF, src/cpu/NewtonSolver.cpp:48-81
+int newton_compF(gs_handle* h, double* norm)
+{
+    Level& L = h->lev[0];
+    {
+        OpScope t(h, GS_OP_RESIDUAL, 0);
+        CU(ks_newton_F(h->cx, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.newtonV, h->newtonF, L.f));
+    }
+    GS(norm_to_host(h, 0));
+    CU(cudaStreamSynchronize(h->stream));
+    *norm = sqrt(*h->h_norm);
+    return GS_OK;
+}
+
+// NewtonSolver::findError, src/cpu/NewtonSolver.cpp:83-108
+int newton_find_error(gs_handle* h, uint64_t* inner)
+{
+    const int nlev = (int)h->lev.size();
+    {
+        OpScope t(h, GS_OP_RESTRICT, 0);
+        // :88-92 — newtonV is NOT restricted to the coarsest level (stays zero there)
+        for (int i = 1; i + 1 < nlev; i++) GS(do_restrict(h, i - 1, h->lev[i - 1].newtonV, h->lev[i].newtonV, nullptr));
+    }
+    for (auto& L : h->lev) L.coef_valid = false;
+    uint64_t cycles = 0;
+    bool conv = false;
+    GS(solve_mg(h, 10, 0.1, false, nullptr, &cycles, &conv));  // :94-100
+    *inner += cycles;
+    Level& L0 = h->lev[0];
+    {
+        OpScope t(h, GS_OP_OTHER, 0);
+        CU(ks_axpy(h->cx, L0.g, 0, L0.g.nzl, L0.newtonV, L0.v, +1));  // :106-107
+    }
+    L0.coef_valid = false;
+    return GS_OK;
+}
+
+int newton_step(gs_handle* h, double* norm, uint64_t* inner)
+{
+    if (!h->newton_begun) GS(newton_begin(h));
+    double tmp;
+    GS(newton_compF(h, &tmp));                    // :21
+    GS(zero_field(h, h->lev[0], h->lev[0].v));    // :22
+    GS(newton_find_error(h, inner));              // :24
+    GS(newton_compF(h, norm));                    // :26
+    return GS_OK;
+}
+
+// NewtonSolver::solve, src/cpu/NewtonSolver.cpp:10-44
+int solve_newton(gs_handle* h, gs_solve_info* info)
+{
+    GS(newton_begin(h));
+    double initial;
+    GS(newton_compF(h, &initial));
+    std::cout << "Inital newton residual: " << initial << '\n';  // printed unconditionally, :16
+    h->history.push_back(initial);
+    info->initial_residual = info->final_residual = initial;
+    for (uint64_t i = 0; i < h->p.maxiter; i++) {
+        auto t0 = std::chrono::high_resolution_clock::now();
+        double res;
+        GS(newton_step(h, &res, &info->inner_cycles));
+        info->iterations++;
+        info->final_residual = res;
+        h->history.push_back(res);
+        std::cout << "newton iter: " << i << " residual: " << res << ' ';
+        std::cout << "Took " << ms_since(t0) << "ms\n";
+        if (reached(res, initial, h->p.tol)) {
+            info->converged = 1;
+            break;
+        }
+    }
+    return GS_OK;
+}
+
+int create_impl(const gs_params* p, int device, int rank, int world, const void* nccl_id, gs_handle** out)
+{
+    if (!p || !out) return fail(GS_EINVAL, "null argument");
+    GS(validate(*p));
+    if (world < 1 || rank < 0 || rank >= world) return fail(GS_EINVAL, "bad rank/world %d/%d", rank, world);
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(GS_EINVAL, "device %d not in [0,%d)", device, ndev);
+    CU(cudaSetDevice(device));
+
+    gs_handle* h = new gs_handle();
+    h->p = *p;
+    h->p.h = 1.0 / (double)(p->dim[1] + 1);  // src/main.cpp:84
+    h->device = device;
+    h->rank = rank;
+    h->world = world;
+    h->newtonF = nullptr;
+    h->newton_begun = false;
+    h->launches = 0;
+    h->opt_kernels = 1;
+    h->opt_graph = 1;
+    h->opt_timing = 0;
+    h->comm = nullptr;
+    h->h_norm = nullptr;
+    memset(h->op_ms, 0, sizeof h->op_ms);
+    memset(h->op_launches, 0, sizeof h->op_launches);
+    for (int i = 0; i < 7; i++) {
+        h->so.dx[i] = p->stencil_off[i][0];
+        h->so.dy[i] = p->stencil_off[i][1];
+        h->so.dz[i] = p->stencil_off[i][2];
+    }
+    h->canonical = canonical_offsets(*p);
+    if (const char* e = getenv("GPUSOLVE_KERNELS")) h->opt_kernels = atoi(e) != 0;
+    if (const char* e = getenv("GPUSOLVE_GRAPH")) h->opt_graph = atoi(e) != 0;
+
+    Partition part = make_partition(*p, world);
+    h->replicated_from = part.replicated_from;
+    const int nlev = part.nlev;
+    h->lev.resize(nlev);
+    h->lvl_ms.assign((size_t)nlev * GS_OP_COUNT, 0.0);
+    h->lvl_launches.assign((size_t)nlev * GS_OP_COUNT, 0);
+    const int ghost = 2;
+    size_t max_blocks = 1;
+    int rc = GS_OK;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    for (int l = 0; l < nlev && rc == GS_OK; l++) {
+        Level& L = h->lev[l];
+        memset(&L, 0, sizeof L);
+        uint64_t n[3];
+        level_dims(*p, l, n);
+        Geom& g = L.g;
+        g.nx = (int)n[0];
+        g.ny = (int)n[1];
+        g.nz = (int)n[2];
+        g.X = g.nx + 2;
+        g.Y = g.ny + 2;
+        g.Zg = g.nz + 2;
+        L.replicated = l >= part.replicated_from;
+        L.zlo = L.replicated ? 0 : part.b[l][rank];
+        L.zhi = L.replicated ? g.Zg : part.b[l][rank + 1];
+        if (world == 1 || L.replicated) {
+            g.z0 = 0;
+            g.nzl = g.Zg;
+        } else {
+            g.z0 = std::max(0, L.zlo - ghost);
+            g.nzl = std::min(g.Zg, L.zhi + ghost) - g.z0;
+        }
+        g.pitch = ((GS_XOFF + g.X + 15) / 16) * 16;
+        g.plane = g.pitch * g.Y;
+        L.count = (size_t)g.plane * g.nzl;
+        // owned interior planes, local indices
+        L.ib = std::max(1, L.zlo) - g.z0;
+        L.ie = std::min(g.nz + 1, L.zhi) - g.z0;
+        L.h = 1.0 / (double)(n[1] + 1);  // src/cpu/CpuGridData.cpp:41 (Y dimension)
+        PointK& k = L.k;
+        for (int i = 0; i < 7; i++) k.c[i] = p->stencil_val[i];
+        k.hh = L.h * L.h;
+        L.pow2 = is_pow2(k.hh);
+        k.inv_hh = L.pow2 ? 1.0 / k.hh : 0.0;
+        k.alpha = (L.h * L.h) / p->stencil_val[0];   // src/cpu/CpuSolver.cpp:145
+        k.preFac = p->stencil_val[0] / (L.h * L.h);  // :144
+        k.omega = p->omega;
+        k.gamma = p->gamma;
+        rc = alloc_zero(&L.v, L.count);
+        if (rc == GS_OK) rc = alloc_zero(&L.vtmp, L.count);
+        if (rc == GS_OK) rc = alloc_zero(&L.f, L.count);
+        if (rc == GS_OK) rc = alloc_zero(&L.r, L.count);
+        if (rc == GS_OK && p->mode == GS_MODE_NONLINEAR) rc = alloc_zero(&L.restV, L.count);
+        if (rc == GS_OK && p->mode == GS_MODE_NEWTON) rc = alloc_zero(&L.newtonV, L.count);
+        if (rc == GS_OK && p->mode == GS_MODE_NEWTON) rc = alloc_zero(&L.coef, L.count);
+        size_t blocks = (size_t)((g.nx + 63) / 64) * ((g.ny + 3) / 4) * (size_t)g.nzl;
+        max_blocks = std::max(max_blocks, blocks);
+    }
+    if (rc == GS_OK && p->mode == GS_MODE_NEWTON) rc = alloc_zero(&h->newtonF, h->lev[0].count);
+    if (rc != GS_OK) {
+        gs_destroy(h);
+        return rc;
+    }
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&h->h_norm, sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&h->cx.norm.partials, max_blocks * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&h->cx.norm.ticket, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&h->cx.norm.result, sizeof(double));
+    if (e == cudaSuccess) e = cudaMemset(h->cx.norm.ticket, 0, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(h->cx.norm.result, 0, sizeof(double));
+    if (e != cudaSuccess) {
+        gs_destroy(h);
+        return fail(GS_ECUDA, "handle setup failed: %s", cudaGetErrorString(e));
+    }
+    h->cx.norm.cap = max_blocks;
+    h->cx.stream = h->stream;
+    h->cx.launches = &h->launches;
+    h->cx.sm_count = prop.multiProcessorCount;
+    h->cx.tune.smooth_variant = 2;
+    h->cx.tune.zchunk = 64;
+    h->cx.tune.fast_min_n = 48;
+    if (const char* ev = getenv("GPUSOLVE_SMOOTH_VARIANT")) h->cx.tune.smooth_variant = atoi(ev);
+    if (const char* ev = getenv("GPUSOLVE_ZCHUNK")) h->cx.tune.zchunk = std::max(1, atoi(ev));
+    if (const char* ev = getenv("GPUSOLVE_FAST_MIN_N")) h->cx.tune.fast_min_n = atoi(ev);
+    e = kf_prepare();
+    if (e != cudaSuccess) {
+        gs_destroy(h);
+        return fail(GS_ECUDA, "kernel setup failed: %s", cudaGetErrorString(e));
+    }
+
+    if (world > 1) {
+        std::vector<int> bounds;
+        for (int l = 0; l < nlev; l++)
+            for (int r = 0; r <= world; r++) bounds.push_back(part.b[l][r]);
+        h->comm = gs_comm_create(rank, world, nccl_id, nlev, bounds.data(), part.replicated_from);
+        if (!h->comm || gs_comm_error(h->comm)[0]) {
+            int code = fail(GS_ECOMM, "communicator setup failed: %s", h->comm ? gs_comm_error(h->comm) : "out of memory");
+            gs_destroy(h);
+            return code;
+        }
+    }
+    // analytic right-hand side on level 0, src/cpu/CpuGridData.cpp:45-78
+    e = ks_init_rhs(h->cx, h->lev[0].g, p->mode, h->p.h, p->gamma, h->lev[0].f);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) {
+        gs_destroy(h);
+        return fail(GS_ECUDA, "right-hand-side initialisation failed: %s", cudaGetErrorString(e));
+    }
+    *out = h;
+    return GS_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------
+extern "C" {
+
+const char* gs_last_error(void) { return g_err; }
+int gs_version(void) { return 100; }
+
+int gs_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return fail(GS_ECUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+    return n;
+}
+
+// src/main.cpp:33-85 — same token order, same operator>> parsing
+int gs_parse_config(const char* path, gs_params* out)
+{
+    if (!path || !out) return fail(GS_EINVAL, "null argument");
+    std::ifstream in(path);
+    if (!in) return fail(GS_EIO, "\"%s\" does not exist or is not a file", path);
+    gs_params p;
+    memset(&p, 0, sizeof p);
+    in >> p.maxiter >> p.tol >> p.dim[0] >> p.dim[1] >> p.dim[2];
+    int mode = -1;
+    in >> mode;
+    p.mode = mode;
+    in >> p.pre >> p.post >> p.omega >> p.gamma;
+    for (int i = 0; i < 7; i++) in >> p.stencil_val[i];
+    for (int d = 0; d < 3; d++)
+        for (int i = 0; i < 7; i++) in >> p.stencil_off[i][d];
+    if (!in) return fail(GS_EINVAL, "config file \"%s\" is truncated or malformed (14 lines expected, README.md:19-33)", path);
+    p.h = 1.0 / (double)(p.dim[1] + 1);
+    p.print_progress = 1;
+    GS(validate(p));
+    *out = p;
+    return GS_OK;
+}
+
+int gs_create(const gs_params* p, int device, gs_handle** out) { return create_impl(p, device, 0, 1, nullptr, out); }
+
+int gs_comm_unique_id(void* buf128)
+{
+    if (!buf128) return fail(GS_EINVAL, "null argument");
+    const char* err = gs_comm_make_id(buf128);
+    if (err) return fail(GS_ECOMM, "%s", err);
+    return GS_OK;
+}
+
+int gs_create_slab(const gs_params* p, int device, int rank, int world, const void* nccl_id, gs_handle** out)
+{
+    if (world > 1 && !nccl_id) return fail(GS_EINVAL, "nccl_id is required when world > 1");
+    return create_impl(p, device, rank, world, nccl_id, out);
+}
+
+int gs_destroy(gs_handle* h)
+{
+    if (!h) return GS_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (auto& kv : h->graphs) cudaGraphExecDestroy(kv.second);
+    for (auto& L : h->lev)
+        for (double* a : {L.v, L.vtmp, L.f, L.r, L.restV, L.newtonV, L.coef})
+            if (a) cudaFree(a);
+    if (h->newtonF) cudaFree(h->newtonF);
+    if (h->cx.norm.partials) cudaFree(h->cx.norm.partials);
+    if (h->cx.norm.ticket) cudaFree(h->cx.norm.ticket);
+    if (h->cx.norm.result) cudaFree(h->cx.norm.result);
+    if (h->h_norm) cudaFreeHost(h->h_norm);
+    for (auto& ep : h->ev_used) {
+        cudaEventDestroy(ep.a);
+        cudaEventDestroy(ep.b);
+    }
+    for (auto e : h->ev_free) cudaEventDestroy(e);
+    if (h->comm) gs_comm_destroy(h->comm);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return GS_OK;
+}
+
+int gs_partition(const gs_params* p, int world, int rank, int level, uint64_t* z_begin, uint64_t* z_end, int* replicated_from)
+{
+    if (!p) return fail(GS_EINVAL, "null argument");
+    GS(validate(*p));
+    if (world < 1 || rank < 0 || rank >= world) return fail(GS_EINVAL, "bad rank/world %d/%d", rank, world);
+    Partition P = make_partition(*p, world);
+    if (level < 0 || level >= P.nlev) return fail(GS_EINVAL, "level %d out of range [0,%d)", level, P.nlev);
+    if (z_begin) *z_begin = (uint64_t)P.b[level][rank];
+    if (z_end) *z_end = (uint64_t)P.b[level][rank + 1];
+    if (level >= P.replicated_from) {
+        if (z_begin) *z_begin = 0;
+        if (z_end) *z_end = (uint64_t)P.b[level][world];
+    }
+    if (replicated_from) *replicated_from = P.replicated_from;
+    return GS_OK;
+}
+
+int gs_num_levels(const gs_handle* h) { return h ? (int)h->lev.size() : fail(GS_EINVAL, "null handle"); }
+
+int gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hval)
+{
+    GS(check_level(h, level));
+    const Level& L = h->lev[level];
+    if (dim) {
+        dim[0] = L.g.nx;
+        dim[1] = L.g.ny;
+        dim[2] = L.g.nz;
+    }
+    if (hval) *hval = L.h;
+    return GS_OK;
+}
+
+// dense host array <-> padded device slab; z-fastest is transposed on the host
+static int field_io(gs_handle* h, int level, int field, double* host, int layout, bool to_host)
+{
+    GS(check_level(h, level));
+    if (!host) return fail(GS_EINVAL, "null host buffer");
+    if (layout != GS_LAYOUT_X_FASTEST && layout != GS_LAYOUT_Z_FASTEST) return fail(GS_EINVAL, "bad layout %d", layout);
+    if (field == GS_FIELD_E) return fail(GS_EUNSUPPORTED, "e is never materialised by the fused kernels; use gs_prolong");
+    double** slot = field_ptr(h, level, field);
+    if (!slot || !*slot) return fail(GS_EINVAL, "field %d does not exist on level %d in mode %d", field, level, h->p.mode);
+    CU(cudaSetDevice(h->device));
+    Level& L = h->lev[level];
+    const Geom& g = L.g;
+    const size_t X = g.X, Y = g.Y, Z = g.Zg;
+    std::vector<double> tmp;
+    double* dense = host;
+    if (layout == GS_LAYOUT_Z_FASTEST) {
+        tmp.resize(X * Y * Z);
+        dense = tmp.data();
+        if (!to_host)
+            for (size_t x = 0; x < X; x++)
+                for (size_t y = 0; y < Y; y++)
+                    for (size_t z = 0; z < Z; z++) dense[x + X * (y + Y * z)] = host[z + Z * (y + Y * x)];
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    if (to_host) {
+        if (partitioned(h, level)) {
+            // every rank returns the whole logical array: gather owned planes through a device staging buffer
+            int rc = gs_comm_gather_to_host(h->comm, *slot, g.plane, g.pitch, g.z0, level, dense, X, Y, Z, h->stream);
+            if (rc != 0) return fail(GS_ECOMM, "field gather failed: %s", gs_comm_error(h->comm));
+        } else {
+            CU(cudaMemcpy2D(dense, X * sizeof(double), *slot + GS_XOFF, g.pitch * sizeof(double), X * sizeof(double), Y * Z,
+                            cudaMemcpyDeviceToHost));
+        }
+        if (layout == GS_LAYOUT_Z_FASTEST)
+            for (size_t x = 0; x < X; x++)
+                for (size_t y = 0; y < Y; y++)
+                    for (size_t z = 0; z < Z; z++) host[z + Z * (y + Y * x)] = dense[x + X * (y + Y * z)];
+    } else {
+        // local planes [z0, z0+nzl) of the dense array (ghost planes included, so they start consistent)
+        const double* src = dense + X * Y * (size_t)g.z0;
+        std::vector<double*> dst = {*slot};
+        if (field == GS_FIELD_V) dst.push_back(L.vtmp);  // keep the halo of both ping-pong buffers identical
+        for (double* d : dst)
+            CU(cudaMemcpy2D(d + GS_XOFF, g.pitch * sizeof(double), src, X * sizeof(double), X * sizeof(double),
+                            Y * (size_t)g.nzl, cudaMemcpyHostToDevice));
+        if (field == GS_FIELD_NEWTONV) L.coef_valid = false;
+        if (field == GS_FIELD_NEWTONF) h->newton_begun = true;
+    }
+    return GS_OK;
+}
+
+int gs_get_field(gs_handle* h, int level, int field, double* host, int layout)
+{
+    return field_io(h, level, field, host, layout, true);
+}
+
+int gs_set_field(gs_handle* h, int level, int field, const double* host, int layout)
+{
+    return field_io(h, level, field, const_cast<double*>(host), layout, false);
+}
+
+// Vector3::dump, src/cpu/Vector3.cpp:56-78
+int gs_dump_field(gs_handle* h, int level, int field, const char* path)
+{
+    GS(check_level(h, level));
+    if (!path) return fail(GS_EINVAL, "null path");
+    const Geom& g = h->lev[level].g;
+    const size_t X = g.X, Y = g.Y, Z = g.Zg;
+    std::vector<double> a(X * Y * Z);
+    GS(gs_get_field(h, level, field, a.data(), GS_LAYOUT_X_FASTEST));
+    std::ofstream out(path);
+    if (!out) return fail(GS_EIO, "cannot open \"%s\" for writing", path);
+    out << X << ' ' << Y << ' ' << Z << '\n';
+    for (size_t x = 0; x < X; x++)
+        for (size_t y = 0; y < Y; y++)
+            for (size_t z = 0; z < Z; z++) out << x << ' ' << y << ' ' << z << ' ' << a[x + X * (y + Y * z)] << '\n';
+    return out ? GS_OK : fail(GS_EIO, "write to \"%s\" failed", path);
+}
+
+int gs_smooth(gs_handle* h, int level, uint64_t iters)
+{
+    GS(check_level(h, level));
+    CU(cudaSetDevice(h->device));
+    return do_smooth(h, level, iters);
+}
+
+int gs_residual(gs_handle* h, int level, double* norm)
+{
+    GS(check_level(h, level));
+    CU(cudaSetDevice(h->device));
+    double n;
+    GS(residual_norm_sync(h, level, true, &n));
+    if (norm) *norm = n;
+    return GS_OK;
+}
+
+int gs_restrict(gs_handle* h, int level, int src_field, int dst_field)
+{
+    GS(check_level(h, level));
+    GS(check_level(h, level + 1));
+    CU(cudaSetDevice(h->device));
+    double** s = field_ptr(h, level, src_field);
+    double** d = field_ptr(h, level + 1, dst_field);
+    if (!s || !*s || !d || !*d) return fail(GS_EINVAL, "field %d/%d not available in mode %d", src_field, dst_field, h->p.mode);
+    OpScope t(h, GS_OP_RESTRICT, level);
+    if (partitioned(h, level)) GS(exchange_halo(h, level, *s, 1));
+    GS(do_restrict(h, level, *s, *d, nullptr));
+    if (dst_field == GS_FIELD_NEWTONV) h->lev[level + 1].coef_valid = false;
+    return GS_OK;
+}
+
+int gs_restrict_residual(gs_handle* h, int level)
+{
+    GS(check_level(h, level));
+    GS(check_level(h, level + 1));
+    CU(cudaSetDevice(h->device));
+    return do_restrict_residual(h, level);
+}
+
+int gs_fas_coarse_rhs(gs_handle* h, int level)
+{
+    GS(check_level(h, level));
+    GS(check_level(h, level + 1));
+    if (h->p.mode != GS_MODE_NONLINEAR) return fail(GS_EINVAL, "gs_fas_coarse_rhs needs mode 1 (CpuSolver.cpp:184 asserts the same)");
+    CU(cudaSetDevice(h->device));
+    return do_fas_coarse_rhs(h, level);
+}
+
+int gs_prolong(gs_handle* h, int level, double* host_e, int layout)
+{
+    GS(check_level(h, level));
+    GS(check_level(h, level + 1));
+    CU(cudaSetDevice(h->device));
+    Level& F = h->lev[level];
+    Level& C = h->lev[level + 1];
+    {
+        OpScope t(h, GS_OP_PROLONG, level);
+        CU(cudaMemsetAsync(F.r, 0, F.count * sizeof(double), h->stream));
+        CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, nullptr, nullptr, C.v, F.r));
+    }
+    return gs_get_field(h, level, GS_FIELD_R, host_e, layout);
+}
+
+int gs_prolong_correct(gs_handle* h, int level)
+{
+    GS(check_level(h, level));
+    GS(check_level(h, level + 1));
+    CU(cudaSetDevice(h->device));
+    return do_prolong_correct(h, level);
+}
+
+int gs_vcycle(gs_handle* h, double* norm)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    CU(cudaSetDevice(h->device));
+    double n;
+    GS(run_vcycle(h, &n));
+    if (norm) *norm = n;
+    return GS_OK;
+}
+
+int gs_newton_compF(gs_handle* h, double* norm)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    if (h->p.mode != GS_MODE_NEWTON) return fail(GS_EINVAL, "gs_newton_compF needs mode 2");
+    CU(cudaSetDevice(h->device));
+    if (!h->newton_begun) GS(newton_begin(h));
+    double n;
+    GS(newton_compF(h, &n));
+    if (norm) *norm = n;
+    return GS_OK;
+}
+
+int gs_newton_step(gs_handle* h, double* norm, uint64_t* inner_cycles)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    if (h->p.mode != GS_MODE_NEWTON) return fail(GS_EINVAL, "gs_newton_step needs mode 2");
+    CU(cudaSetDevice(h->device));
+    double n;
+    uint64_t inner = 0;
+    GS(newton_step(h, &n, &inner));
+    if (norm) *norm = n;
+    if (inner_cycles) *inner_cycles = inner;
+    return GS_OK;
+}
+
+int gs_solve(gs_handle* h, gs_solve_info* info)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    CU(cudaSetDevice(h->device));
+    gs_solve_info local;
+    memset(&local, 0, sizeof local);
+    h->history.clear();
+    int rc;
+    if (h->p.mode == GS_MODE_NEWTON) {
+        rc = solve_newton(h, &local);
+    } else {
+        bool conv = false;
+        rc = solve_mg(h, h->p.maxiter, h->p.tol, h->p.print_progress != 0, &h->history, &local.iterations, &conv);
+        local.converged = conv;
+        if (!h->history.empty()) {
+            local.initial_residual = h->history.front();
+            local.final_residual = h->history.back();
+        }
+    }
+    std::cout.flush();
+    if (info) *info = local;
+    return rc;
+}
+
+int gs_get_history(const gs_handle* h, double* norms, int cap, int* count)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    int n = (int)h->history.size();
+    if (count) *count = n;
+    if (norms)
+        for (int i = 0; i < n && i < cap; i++) norms[i] = h->history[i];
+    return GS_OK;
+}
+
+int gs_reset_timing(gs_handle* h)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    CU(cudaStreamSynchronize(h->stream));
+    for (auto& ep : h->ev_used) {
+        h->ev_free.push_back(ep.a);
+        h->ev_free.push_back(ep.b);
+    }
+    h->ev_used.clear();
+    memset(h->op_ms, 0, sizeof h->op_ms);
+    memset(h->op_launches, 0, sizeof h->op_launches);
+    std::fill(h->lvl_ms.begin(), h->lvl_ms.end(), 0.0);
+    std::fill(h->lvl_launches.begin(), h->lvl_launches.end(), 0);
+    return GS_OK;
+}
+
+static int drain_events(gs_handle* h)
+{
+    CU(cudaStreamSynchronize(h->stream));
+    for (auto& ep : h->ev_used) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, ep.a, ep.b) == cudaSuccess) {
+            h->op_ms[ep.op] += t;
+            h->lvl_ms[(size_t)ep.level * GS_OP_COUNT + ep.op] += t;
+        }
+        h->ev_free.push_back(ep.a);
+        h->ev_free.push_back(ep.b);
+    }
+    h->ev_used.clear();
+    return GS_OK;
+}
+
+int gs_get_level_timing(gs_handle* h, int level, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT])
+{
+    GS(check_level(h, level));
+    GS(drain_events(h));
+    for (int i = 0; i < GS_OP_COUNT; i++) {
+        if (ms) ms[i] = h->lvl_ms[(size_t)level * GS_OP_COUNT + i];
+        if (launches) launches[i] = h->lvl_launches[(size_t)level * GS_OP_COUNT + i];
+    }
+    return GS_OK;
+}
+
+int gs_get_timing(gs_handle* h, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT])
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    GS(drain_events(h));
+    for (int i = 0; i < GS_OP_COUNT; i++) {
+        if (ms) ms[i] = h->op_ms[i];
+        if (launches) launches[i] = h->op_launches[i];
+    }
+    return GS_OK;
+}
+
+uint64_t gs_launch_count(const gs_handle* h) { return h ? h->launches : 0; }
+
+int gs_set_option(gs_handle* h, const char* name, int64_t value)
+{
+    if (!h || !name) return fail(GS_EINVAL, "null argument");
+    std::string n(name);
+    if (n == "kernels") {
+        h->opt_kernels = value != 0;
+        for (auto& L : h->lev) L.coef_valid = false;
+    } else if (n == "graph") h->opt_graph = value != 0;
+    else if (n == "timing") h->opt_timing = value != 0;
+    else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
+    else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
+    else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
+    else return fail(GS_EINVAL, "unknown option \"%s\"", name);
+    return GS_OK;
+}
+
+void* gs_stream(gs_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+int gs_synchronize(gs_handle* h)
+{
+    if (!h) return fail(GS_EINVAL, "null handle");
+    CU(cudaStreamSynchronize(h->stream));
+    return GS_OK;
+}
+
+}  // extern "C"

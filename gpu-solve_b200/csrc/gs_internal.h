@@ -1,0 +1,108 @@
+// gs_internal.h — data structures shared by the C-ABI layer (gs_api.cu) and the
+// kernel translation units.  Nothing here crosses the C ABI.
+//
+// Device layout of every level array (DESIGN.md "Data layout in HBM"):
+//   x fastest, row pitch padded to a multiple of 16 doubles with logical x = 1
+//   (first interior column) on a 128-byte boundary:  elem(x,y,zl) =
+//   GS_XOFF + x + pitch*y + plane*zl,  plane = pitch*Y.  The one-cell Dirichlet
+//   halo of the reference (src/cpu/CpuGridData.cpp:32-36) is materialised and
+//   stays zero.  `zl` is a LOCAL plane: a rank holds global planes
+//   [z0, z0 + nzl) of the (nz+2) logical planes (all of them on one GPU).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gpusolve_cuda.h"
+
+#define GS_XOFF 15  // doubles in front of logical x = 0, so that x = 1 sits at element 16
+
+typedef long long i64;
+
+struct Geom {
+    int X, Y, Zg;    // logical array dims (n + 2) of the whole level
+    int nx, ny, nz;  // interior points of the whole level
+    int z0;          // global plane index of local plane 0
+    int nzl;         // local planes held
+    i64 pitch;       // doubles per row
+    i64 plane;       // doubles per plane (= pitch * Y)
+};
+
+__host__ __device__ __forceinline__ i64 gs_idx(const Geom& g, int x, int y, int zl)
+{
+    return (i64)GS_XOFF + x + g.pitch * y + g.plane * (i64)zl;
+}
+
+// per-level constants of the point update, computed on the host exactly as the
+// reference does (src/cpu/CpuSolver.cpp:144-145)
+struct PointK {
+    double c[7];     // stencil values, config order
+    double hh;       // level.h * level.h
+    double inv_hh;   // 1/hh, only used when hh is a power of two (then s*inv_hh == s/hh bit for bit)
+    double alpha;    // (h*h)/c[0]
+    double preFac;   // c[0]/(h*h)
+    double omega, gamma;
+};
+
+struct StencilOff {
+    int dx[7], dy[7], dz[7];
+};
+
+// kernel "mode" template values
+enum { KM_LINEAR = 0, KM_NONLINEAR = 1, KM_NEWTON_EXP = 2, KM_NEWTON_COEF = 3 };
+
+// device-side scratch for deterministic norms (fixed-order two-stage reduction)
+struct NormBuf {
+    double* partials;     // one slot per CTA of the reducing kernel
+    unsigned int* ticket; // last-CTA-done counter (self-resetting)
+    double* result;       // device scalar: sum of squares
+    size_t cap;           // slots in partials
+};
+
+// run-time tuning knobs (gs_set_option / GPUSOLVE_* environment)
+struct Tune {
+    int smooth_variant;  // 0 simple, 1x z-march through L1, 2x TMA-staged z-march (kernels_fast.cu)
+    int zchunk;          // planes per CTA of the z-marching kernels
+    int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
+};
+
+struct LaunchCtx {
+    cudaStream_t stream;
+    Tune tune;
+    NormBuf norm;
+    uint64_t* launches;   // host counter of kernels launched
+    int sm_count;
+};
+
+// ---- kernels_simple.cu: one thread per lattice point, any 7 in-range offsets ----
+// All take LOCAL plane ranges [zb, ze) of points to update.
+cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                      const StencilOff& so, const double* vin, double* vout, const double* f, const double* aux);
+// r = f - A(v) (stored if r != nullptr) and sum of squares -> cx.norm.result
+cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                        const StencilOff& so, const double* v, const double* f, const double* aux, double* r);
+// coarse(interior) = full weighting of fine; coarse local planes [zb, ze)
+cudaError_t ks_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* fine,
+                        double* coarse, double* coarse2);
+// vout = vin + P(coarse v [- coarse restV]) on fine local planes [zb, ze); e_out (optional) receives e
+cudaError_t ks_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
+                               double* vout, const double* coarse, double* e_out);
+// FAS: f += A(restV)/hh + gamma*restV*exp(restV)   (r_out optional: receives A(restV) like the reference's r)
+cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                       const StencilOff& so, const double* restv, double* f, double* r_out);
+// Newton F: f = newtonF - (A(nv)/hh + gamma*nv*exp(nv)), sum of squares -> cx.norm.result
+cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                        const StencilOff& so, const double* nv, const double* newtonF, double* f);
+// coef = (gamma*(1+nv))*exp(nv) over interior
+cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, double gamma, const double* nv,
+                           double* coef);
+// dst = dst + sign*src over interior points of local planes [zb, ze)
+cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* dst, const double* src, int sign);
+// analytic right-hand side, src/cpu/CpuGridData.cpp:45-78 (local planes [0, nzl))
+cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f);
+
+// ---- kernels_fast.cu: tuned sm_100a kernels for the canonical axis-aligned stencil ----
+bool kf_available();
+// one-time per-process setup (dynamic shared memory attributes); call outside stream capture
+cudaError_t kf_prepare();
+cudaError_t kf_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                      const double* vin, double* vout, const double* f, const double* aux, bool* handled);

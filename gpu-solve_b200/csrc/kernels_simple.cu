@@ -1,0 +1,484 @@
+// kernels_simple.cu — one thread per lattice point, any seven in-range stencil
+// offsets in config order.  These are the general-purpose kernels (arbitrary
+// offsets, every mode) and the in-library cross-check of the tuned kernels in
+// kernels_fast.cu.  They are CUDA kernels for sm_100a, not a CPU fallback.
+//
+// Arithmetic contract (DESIGN.md "Parity"): the library is compiled with
+// -fmad=false, so every expression below is evaluated with separate IEEE fp64
+// multiplies and adds in the order written, which is the order of the reference
+// (cited per function, paths relative to the reference root).  Linear-mode
+// fields are therefore bit-identical to GpuSolve-cpu; modes with exp() differ by
+// CUDA-vs-glibc exp rounding only.
+#include "gs_internal.h"
+
+namespace {
+
+constexpr int BX = 64, BY = 4;  // 256 threads, one x-row of 64 points per 2 warps
+
+struct SmoothP {
+    Geom g;
+    PointK k;
+    i64 toff[7];
+    int zb;
+    const double* vin;
+    double* vout;
+    const double* f;
+    const double* aux;
+};
+
+__device__ __forceinline__ double tap_sum(const double* __restrict__ a, i64 c, const double (&cv)[7], const i64 (&toff)[7])
+{
+    // src/cpu/CpuSolver.cpp:56-60: stencilsum = 0.0; stencilsum += values[i] * v(p + o_i), i ascending
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 7; i++) s += cv[i] * a[c + toff[i]];
+    return s;
+}
+
+// s -> r = f - (s/(h*h) + NL), and the Jacobi denominator (modes 1..3)
+// src/cpu/CpuSolver.cpp:61-74 (residual) and :161-171 (denominator)
+template <int KM, bool POW2>
+__device__ __forceinline__ double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
+{
+    s = POW2 ? s * k.inv_hh : s / k.hh;
+    den = 0.0;
+    if (KM == KM_NONLINEAR) {
+        double ex = exp(vc);
+        double nl = (k.gamma * vc) * ex;
+        s += nl;
+        den = k.preFac + (k.gamma * (1 + vc)) * ex;
+    } else if (KM == KM_NEWTON_EXP) {
+        double ex = exp(aux);
+        double g1 = k.gamma * (1 + aux);
+        s += (g1 * vc) * ex;
+        den = k.preFac + g1 * ex;
+    } else if (KM == KM_NEWTON_COEF) {
+        // aux = (gamma*(1+nv))*exp(nv) precomputed once per Newton step (ks_newton_coef);
+        // (g1*ex)*v instead of (g1*v)*ex: one rounding apart, inside the exp() tolerance
+        s += aux * vc;
+        den = k.preFac + aux;
+    }
+    return fc - s;
+}
+
+template <int KM>
+__device__ __forceinline__ double jacobi_update(double vc, double r, double den, const PointK& k)
+{
+    // src/cpu/CpuSolver.cpp:158 resp. :164,:171
+    if (KM == KM_LINEAR) return vc + k.omega * (k.alpha * r);
+    return vc + k.omega * (r / den);
+}
+
+template <int KM, bool POW2>
+__global__ void __launch_bounds__(BX* BY) smooth_simple(SmoothP p)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + p.zb;
+    if (x > p.g.nx || y > p.g.ny) return;
+    const i64 c = gs_idx(p.g, x, y, zl);
+    const double vc = p.vin[c];
+    double s = tap_sum(p.vin, c, p.k.c, p.toff);
+    const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
+    double den;
+    const double r = finish_residual<KM, POW2>(s, vc, p.f[c], aux, p.k, den);
+    p.vout[c] = jacobi_update<KM>(vc, r, den, p.k);
+}
+
+// ---- deterministic sum of squares: CTA tree, then the last CTA to finish adds
+// the per-CTA partials in index order with the same tree (no fp atomics) ----
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int NT>
+__device__ __forceinline__ double block_sum(double v, double* sh)
+{
+    const int tid = threadIdx.x + threadIdx.y * blockDim.x;
+    v = warp_sum(v);
+    if ((tid & 31) == 0) sh[tid >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (tid < 32) {
+        t = tid < NT / 32 ? sh[tid] : 0.0;
+        t = warp_sum(t);
+    }
+    __syncthreads();
+    return t;  // valid in thread 0
+}
+
+template <int NT>
+__device__ __forceinline__ void grid_sum_finish(double block_total, NormBuf nb, double* sh)
+{
+    const int tid = threadIdx.x + threadIdx.y * blockDim.x;
+    const unsigned nblk = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned bid = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    __shared__ bool last;
+    if (tid == 0) {
+        nb.partials[bid] = block_total;
+        __threadfence();
+        unsigned t = atomicAdd(nb.ticket, 1u);
+        last = (t == nblk - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double acc = 0.0;
+    for (unsigned i = tid; i < nblk; i += NT) acc += __ldcg(&nb.partials[i]);
+    double tot = block_sum<NT>(acc, sh);
+    if (tid == 0) {
+        *nb.result = tot;
+        *nb.ticket = 0u;
+    }
+}
+
+struct ResidP {
+    Geom g;
+    PointK k;
+    i64 toff[7];
+    int zb;
+    const double* v;
+    const double* f;
+    const double* aux;
+    double* r;
+    NormBuf nb;
+};
+
+// CpuSolver::compResidual, src/cpu/CpuSolver.cpp:45-83
+template <int KM, bool POW2>
+__global__ void __launch_bounds__(BX* BY) residual_simple(ResidP p)
+{
+    __shared__ double sh[32];
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + p.zb;
+    double sq = 0.0;
+    if (x <= p.g.nx && y <= p.g.ny) {
+        const i64 c = gs_idx(p.g, x, y, zl);
+        const double vc = p.v[c];
+        double s = tap_sum(p.v, c, p.k.c, p.toff);
+        const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
+        double den;
+        const double r = finish_residual<KM, POW2>(s, vc, p.f[c], aux, p.k, den);
+        if (p.r) p.r[c] = r;
+        sq = r * r;
+    }
+    double tot = block_sum<BX * BY>(sq, sh);
+    grid_sum_finish<BX * BY>(tot, p.nb, sh);
+}
+
+struct RestrictP {
+    Geom gf, gc;
+    int zb;
+    const double* fine;
+    double* coarse;
+    double* coarse2;
+};
+
+// CpuSolver::restrict, src/cpu/CpuSolver.cpp:211-238: running sum over the 27
+// neighbours, x offset outermost, z offset innermost, weights 0.125*w*w*w
+__global__ void __launch_bounds__(BX* BY) restrict_simple(RestrictP p)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zc = blockIdx.z + p.zb;  // local coarse plane
+    if (x > p.gc.nx || y > p.gc.ny) return;
+    const int zf = 2 * (zc + p.gc.z0) - p.gf.z0;  // local fine plane of the centre
+    const i64 fc = gs_idx(p.gf, 2 * x, 2 * y, zf);
+    const double w[3] = {0.5, 1.0, 0.5};
+    double acc = 0.0;
+#pragma unroll
+    for (int ii = -1; ii < 2; ii++)
+#pragma unroll
+        for (int jj = -1; jj < 2; jj++)
+#pragma unroll
+            for (int kk = -1; kk < 2; kk++) {
+                const double fac = 0.125 * w[ii + 1] * w[jj + 1] * w[kk + 1];
+                acc += fac * p.fine[fc + ii + jj * p.gf.pitch + kk * p.gf.plane];
+            }
+    const i64 cc = gs_idx(p.gc, x, y, zc);
+    p.coarse[cc] = acc;
+    if (p.coarse2) p.coarse2[cc] = acc;
+}
+
+struct ProlongP {
+    Geom gf, gc;
+    int zb;
+    const double* vin;
+    double* vout;
+    const double* coarse;
+    double* e_out;
+};
+
+// CpuSolver::interpolate (src/cpu/CpuSolver.cpp:240-290) in closed form, then
+// v += e (:131-132).  The four dependent passes of the reference (inject, x, y, z
+// averages) nest as  e = avg_z(avg_y(avg_x(C)))  with avg = 0.5*a + 0.5*b on odd
+// indices and identity on even ones; same operations, same order => same bits.
+__device__ __forceinline__ double prolong_point(const double* __restrict__ cv, const Geom& gc, int X, int Y, int Zg)
+{
+    const int i = X >> 1, j = Y >> 1, k = (Zg >> 1) - gc.z0;
+    const bool ox = X & 1, oy = Y & 1, oz = Zg & 1;
+    const i64 b = gs_idx(gc, i, j, k);
+    auto ax = [&](i64 q) { return ox ? 0.5 * cv[q] + 0.5 * cv[q + 1] : cv[q]; };
+    auto ay = [&](i64 q) { return oy ? 0.5 * ax(q) + 0.5 * ax(q + gc.pitch) : ax(q); };
+    return oz ? 0.5 * ay(b) + 0.5 * ay(b + gc.plane) : ay(b);
+}
+
+__global__ void __launch_bounds__(BX* BY) prolong_correct_simple(ProlongP p)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + p.zb;
+    if (x > p.gf.nx || y > p.gf.ny) return;
+    const double e = prolong_point(p.coarse, p.gc, x, y, zl + p.gf.z0);
+    const i64 c = gs_idx(p.gf, x, y, zl);
+    if (p.e_out) p.e_out[c] = e;
+    if (p.vout) p.vout[c] = p.vin[c] + e;
+}
+
+struct FasP {
+    Geom g;
+    PointK k;
+    i64 toff[7];
+    int zb;
+    const double* restv;
+    double* f;
+    double* r_out;
+};
+
+// CpuSolver::applyStencil (src/cpu/CpuSolver.cpp:182-209) on restV, then f += r (:112)
+template <bool POW2>
+__global__ void __launch_bounds__(BX* BY) fas_rhs_simple(FasP p)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + p.zb;
+    if (x > p.g.nx || y > p.g.ny) return;
+    const i64 c = gs_idx(p.g, x, y, zl);
+    const double vc = p.restv[c];
+    double s = tap_sum(p.restv, c, p.k.c, p.toff);
+    s = POW2 ? s * p.k.inv_hh : s / p.k.hh;
+    const double nl = (p.k.gamma * vc) * exp(vc);
+    s += nl;
+    if (p.r_out) p.r_out[c] = s;
+    p.f[c] = p.f[c] + s;
+}
+
+struct NewtonFP {
+    Geom g;
+    PointK k;
+    i64 toff[7];
+    int zb;
+    const double* nv;
+    const double* newtonF;
+    double* f;
+    NormBuf nb;
+};
+
+// NewtonSolver::compF, src/cpu/NewtonSolver.cpp:48-81
+template <bool POW2>
+__global__ void __launch_bounds__(BX* BY) newton_F_simple(NewtonFP p)
+{
+    __shared__ double sh[32];
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + p.zb;
+    double sq = 0.0;
+    if (x <= p.g.nx && y <= p.g.ny) {
+        const i64 c = gs_idx(p.g, x, y, zl);
+        const double vc = p.nv[c];
+        double s = tap_sum(p.nv, c, p.k.c, p.toff);
+        s = POW2 ? s * p.k.inv_hh : s / p.k.hh;
+        const double ex = exp(vc);
+        const double nl = (p.k.gamma * vc) * ex;
+        s += nl;
+        const double fv = p.newtonF[c] - s;
+        p.f[c] = fv;
+        sq = fv * fv;
+    }
+    double tot = block_sum<BX * BY>(sq, sh);
+    grid_sum_finish<BX * BY>(tot, p.nb, sh);
+}
+
+__global__ void __launch_bounds__(BX* BY) newton_coef_simple(Geom g, int zb, double gamma, const double* __restrict__ nv,
+                                                              double* __restrict__ coef)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + zb;
+    if (x > g.nx || y > g.ny) return;
+    const i64 c = gs_idx(g, x, y, zl);
+    const double n = nv[c];
+    coef[c] = (gamma * (1 + n)) * exp(n);
+}
+
+// Vector3::operator+= / -= (src/cpu/Vector3.cpp:34-54); the halo of every src
+// operand the V-cycle uses is zero, so the interior is the whole effect
+__global__ void __launch_bounds__(BX* BY) axpy_simple(Geom g, int zb, double* __restrict__ dst, const double* __restrict__ src,
+                                                       int sign)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zl = blockIdx.z + zb;
+    if (x > g.nx || y > g.ny) return;
+    const i64 c = gs_idx(g, x, y, zl);
+    dst[c] = sign >= 0 ? dst[c] + src[c] : dst[c] - src[c];
+}
+
+// src/cpu/CpuGridData.cpp:7-12
+__device__ __forceinline__ double rhs_f0(double x)
+{
+    return (100 * x * (x - 1.0) * x * (x - 1.0) * x * (x - 1.0) * x * (x - 1.0));
+}
+__device__ __forceinline__ double rhs_f2(double x)
+{
+    return (100.0 * 4.0 * (x - 1.0) * (x - 1.0) * x * x * (14.0 * x * x - 14.0 * x + 3));
+}
+
+// src/cpu/CpuGridData.cpp:45-78.  Linear: interior only, sampled at the zero-based
+// interior index (:47-58).  Otherwise: whole array, sampled at the array index (:62-76).
+__global__ void __launch_bounds__(BX* BY) init_rhs_simple(Geom g, int mode, double h, double gamma, double* __restrict__ f)
+{
+    const int x = blockIdx.x * BX + threadIdx.x;
+    const int y = blockIdx.y * BY + threadIdx.y;
+    const int zl = blockIdx.z;
+    const int zg = zl + g.z0;
+    if (x >= g.X || y >= g.Y) return;
+    if (mode == GS_MODE_LINEAR) {
+        if (x < 1 || x > g.nx || y < 1 || y > g.ny || zg < 1 || zg > g.nz) return;
+        const double px = (x - 1) * h, py = (y - 1) * h, pz = (zg - 1) * h;
+        const double val = -(rhs_f2(px) * rhs_f0(py) * rhs_f0(pz) + rhs_f0(px) * rhs_f2(py) * rhs_f0(pz) +
+                             rhs_f0(px) * rhs_f0(py) * rhs_f2(pz));
+        f[gs_idx(g, x, y, zl)] = val;
+    } else {
+        if (zg < 0 || zg >= g.Zg) return;
+        const double px = x * h, py = y * h, pz = zg * h;
+        const double val = 2.0 * ((py - py * py) * (pz - pz * pz) + (px - px * px) * (pz - pz * pz) + (px - px * px) * (py - py * py)) +
+                           gamma * (px - px * px) * (py - py * py) * (pz - pz * pz) *
+                               exp((px - px * px) * (py - py * py) * (pz - pz * pz));
+        f[gs_idx(g, x, y, zl)] = val;
+    }
+}
+
+inline dim3 grid_for(int nx, int ny, int nz) { return dim3((nx + BX - 1) / BX, (ny + BY - 1) / BY, nz); }
+
+inline void fill_toff(const Geom& g, const StencilOff& so, i64 (&toff)[7])
+{
+    for (int i = 0; i < 7; i++) toff[i] = so.dx[i] + so.dy[i] * g.pitch + so.dz[i] * g.plane;
+}
+
+inline cudaError_t done(const LaunchCtx& cx)
+{
+    if (cx.launches) ++*cx.launches;
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+#define KM_DISPATCH(KERNEL, km, pow2, ...)                                                          \
+    do {                                                                                            \
+        if (pow2) {                                                                                 \
+            switch (km) {                                                                           \
+            case KM_LINEAR: KERNEL<KM_LINEAR, true> __VA_ARGS__; break;                             \
+            case KM_NONLINEAR: KERNEL<KM_NONLINEAR, true> __VA_ARGS__; break;                       \
+            case KM_NEWTON_EXP: KERNEL<KM_NEWTON_EXP, true> __VA_ARGS__; break;                     \
+            default: KERNEL<KM_NEWTON_COEF, true> __VA_ARGS__; break;                               \
+            }                                                                                       \
+        } else {                                                                                    \
+            switch (km) {                                                                           \
+            case KM_LINEAR: KERNEL<KM_LINEAR, false> __VA_ARGS__; break;                            \
+            case KM_NONLINEAR: KERNEL<KM_NONLINEAR, false> __VA_ARGS__; break;                      \
+            case KM_NEWTON_EXP: KERNEL<KM_NEWTON_EXP, false> __VA_ARGS__; break;                    \
+            default: KERNEL<KM_NEWTON_COEF, false> __VA_ARGS__; break;                              \
+            }                                                                                       \
+        }                                                                                           \
+    } while (0)
+
+cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                      const StencilOff& so, const double* vin, double* vout, const double* f, const double* aux)
+{
+    if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaSuccess;
+    SmoothP p{g, k, {}, zb, vin, vout, f, aux};
+    fill_toff(g, so, p.toff);
+    dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
+    KM_DISPATCH(smooth_simple, km, pow2, <<<grid, block, 0, cx.stream>>>(p));
+    return done(cx);
+}
+
+cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                        const StencilOff& so, const double* v, const double* f, const double* aux, double* r)
+{
+    if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaErrorInvalidValue;
+    ResidP p{g, k, {}, zb, v, f, aux, r, cx.norm};
+    fill_toff(g, so, p.toff);
+    dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
+    if ((size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaErrorInvalidValue;
+    KM_DISPATCH(residual_simple, km, pow2, <<<grid, block, 0, cx.stream>>>(p));
+    return done(cx);
+}
+
+cudaError_t ks_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* fine,
+                        double* coarse, double* coarse2)
+{
+    if (ze <= zb || gc.nx <= 0 || gc.ny <= 0) return cudaSuccess;
+    RestrictP p{gf, gc, zb, fine, coarse, coarse2};
+    restrict_simple<<<grid_for(gc.nx, gc.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
+    return done(cx);
+}
+
+cudaError_t ks_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
+                               double* vout, const double* coarse, double* e_out)
+{
+    if (ze <= zb) return cudaSuccess;
+    ProlongP p{gf, gc, zb, vin, vout, coarse, e_out};
+    prolong_correct_simple<<<grid_for(gf.nx, gf.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
+    return done(cx);
+}
+
+cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                       const StencilOff& so, const double* restv, double* f, double* r_out)
+{
+    if (ze <= zb) return cudaSuccess;
+    FasP p{g, k, {}, zb, restv, f, r_out};
+    fill_toff(g, so, p.toff);
+    dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
+    if (pow2) fas_rhs_simple<true><<<grid, block, 0, cx.stream>>>(p);
+    else fas_rhs_simple<false><<<grid, block, 0, cx.stream>>>(p);
+    return done(cx);
+}
+
+cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                        const StencilOff& so, const double* nv, const double* newtonF, double* f)
+{
+    if (ze <= zb) return cudaErrorInvalidValue;
+    NewtonFP p{g, k, {}, zb, nv, newtonF, f, cx.norm};
+    fill_toff(g, so, p.toff);
+    dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
+    if ((size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaErrorInvalidValue;
+    if (pow2) newton_F_simple<true><<<grid, block, 0, cx.stream>>>(p);
+    else newton_F_simple<false><<<grid, block, 0, cx.stream>>>(p);
+    return done(cx);
+}
+
+cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, double gamma, const double* nv, double* coef)
+{
+    if (ze <= zb) return cudaSuccess;
+    newton_coef_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, gamma, nv, coef);
+    return done(cx);
+}
+
+cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* dst, const double* src, int sign)
+{
+    if (ze <= zb) return cudaSuccess;
+    axpy_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, dst, src, sign);
+    return done(cx);
+}
+
+cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f)
+{
+    init_rhs_simple<<<grid_for(g.X, g.Y, g.nzl), dim3(BX, BY), 0, cx.stream>>>(g, mode, h, gamma, f);
+    return done(cx);
+}

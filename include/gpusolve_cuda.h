@@ -173,11 +173,15 @@ int  gs_get_history(const gs_handle* h, double* norms, int cap, int* count);
 /* ---- timing / tuning */
 int  gs_reset_timing(gs_handle* h);
 int  gs_get_timing(gs_handle* h, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT]);
+/* the same, for one level (the level an operator is called ON: restriction from l to l+1 counts on l) */
+int  gs_get_level_timing(gs_handle* h, int level, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT]);
 /* total kernels launched by this handle since creation */
 uint64_t gs_launch_count(const gs_handle* h);
-/* options: "kernels" = 0 simple reference kernels, 1 tuned (default);
+/* options: "kernels" = 0 simple one-thread-per-point kernels, 1 tuned (default);
  *          "graph"   = 0/1 capture the V-cycle in a CUDA graph (default 1);
- *          "timing"  = 0/1 per-operator CUDA events (default 0, disables graph) */
+ *          "timing"  = 0/1 per-operator CUDA events (default 0, disables graph);
+ *          "smooth_variant", "zchunk", "fast_min_n" = kernel tuning knobs
+ *          (gpu-solve_b200/csrc/kernels_fast.cu), also GPUSOLVE_* environment */
 int  gs_set_option(gs_handle* h, const char* name, int64_t value);
 /* the CUDA stream all work of this handle is issued on (a cudaStream_t) */
 void* gs_stream(gs_handle* h);

@@ -1,0 +1,132 @@
+"""CPU suite: the C-ABI library loads, exports every symbol include/gpusolve_cuda.h declares,
+and its host-side logic (config parser, validation, slab partition) behaves like the
+reference driver (src/main.cpp).  No compute calls: there is no GPU here and no CPU fallback."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from cases import GOLDEN_DIR, ROOT
+
+HEADER = os.path.join(ROOT, "include", "gpusolve_cuda.h")
+CONF = os.path.join(GOLDEN_DIR, "data-2nd_order.conf")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gs_[A-Za-z_0-9]+)\s*\(", src)))
+
+
+def test_header_declares_a_reasonable_surface():
+    syms = declared_symbols()
+    for must in ("gs_create", "gs_solve", "gs_smooth", "gs_residual", "gs_restrict_residual", "gs_prolong_correct",
+                 "gs_vcycle", "gs_newton_step", "gs_get_field", "gs_set_field", "gs_destroy", "gs_last_error"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(gs):
+    lib = C.CDLL(gs.LIB)
+    for name in declared_symbols():
+        assert hasattr(lib, name), f"{name} declared in gpusolve_cuda.h but not exported"
+    assert set(gs.SIGNATURES) == set(declared_symbols()), "python binding and header drifted apart"
+
+
+def test_library_has_sm100a_code_and_no_nccl_link_dependency(gs):
+    out = subprocess.run(["cuobjdump", "-lelf", gs.LIB], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
+    needed = subprocess.run(["readelf", "-d", gs.LIB], capture_output=True, text=True).stdout
+    assert "libnccl" not in needed  # bound with dlopen only when world > 1
+
+
+def test_parse_shipped_config(gs):
+    p = gs.parse_config(CONF)
+    assert (p.maxiter, p.tol, tuple(p.dim), p.mode, p.pre, p.post) == (10, 1e-5, (127, 127, 127), 2, 3, 3)
+    assert (p.omega, p.gamma) == (0.8, 1.0)
+    assert p.h == 1.0 / 128  # src/main.cpp:84
+    assert list(p.stencil_val) == [6, -1, -1, -1, -1, -1, -1]
+    assert [tuple(o) for o in p.stencil_off] == list(gs.CANONICAL_OFFSETS)
+    assert p.print_progress == 1
+
+
+def _write(tmp_path, lines):
+    f = tmp_path / "c.conf"
+    f.write_text("\n".join(lines) + "\n")
+    return f
+
+
+BASE = ["10", "10e-5", "15 15 15", "0", "2", "2", "0.8", "1.0", "6 -1 -1 -1 -1 -1 -1", "0 1 -1 0 0 0 0", "0 0 0 1 -1 0 0",
+        "0 0 0 0 0 1 -1"]
+
+
+def test_parser_is_whitespace_driven_like_operator_shift(gs, tmp_path):
+    p = gs.parse_config(_write(tmp_path, BASE))  # dims on one line, "10e-5" as runExperiments.py writes it
+    assert tuple(p.dim) == (15, 15, 15) and p.tol == 10e-5
+
+
+@pytest.mark.parametrize("mutate,needle", [
+    (lambda l: l[:3] + ["7"] + l[4:], "Invalid mode"),
+    (lambda l: l[:-1] + ["0 0 0 0 0 2 -1"], "outside {-1,0,1}"),
+    (lambda l: l[:-2], "truncated"),
+    (lambda l: l[:2] + ["0 15 15"] + l[3:], "out of range"),
+])
+def test_parser_rejects_bad_configs(gs, tmp_path, mutate, needle):
+    with pytest.raises(gs.GpuSolveError, match=re.escape(needle)):
+        gs.parse_config(_write(tmp_path, mutate(list(BASE))))
+
+
+def test_missing_config_file(gs, tmp_path):
+    with pytest.raises(gs.GpuSolveError, match="does not exist"):
+        gs.parse_config(tmp_path / "nope.conf")
+
+
+def test_create_fails_loudly_without_a_gpu(gs):
+    if gs.load().gs_device_count() > 0:
+        pytest.skip("a GPU is visible")
+    with pytest.raises(gs.GpuSolveError):
+        gs.GpuSolve(gs.make_params(7))
+
+
+def test_driver_binary_usage(gs):
+    assert os.path.exists(gs.EXE)
+    r = subprocess.run([gs.EXE], capture_output=True, text=True)
+    assert r.returncode == 1 and "Missing config file" in r.stderr
+    r = subprocess.run([gs.EXE, "/nonexistent.conf"], capture_output=True, text=True)
+    assert r.returncode == 1 and "does not exist or is not a file" in r.stderr
+
+
+@pytest.mark.parametrize("n,world", [(1023, 8), (1023, 4), (1023, 2), (511, 8), (511, 2), (127, 2), (255, 3), (100, 4), (63, 8)])
+def test_partition_is_a_coarse_aligned_cover(gs, n, world):
+    p = gs.make_params(n)
+    import math
+    nlev = int(math.floor(math.log(n) / math.log(2.0))) + 1
+    _, _, rep = gs.partition(p, world, 0, 0)
+    assert 0 <= rep <= nlev - 2 or rep == 0
+    dims = n
+    for level in range(nlev):
+        Z = dims + 2
+        prev_end = 0
+        for r in range(world):
+            zb, ze, rep2 = gs.partition(p, world, r, level)
+            assert rep2 == rep
+            if level >= rep:
+                assert (zb, ze) == (0, Z)  # replicated: every rank holds the whole level
+                continue
+            assert zb == prev_end and ze > zb, "slabs must tile [0, Z) without gaps"
+            prev_end = ze
+            if level + 1 < rep:
+                cb, ce, _ = gs.partition(p, world, r, level + 1)
+                assert zb == 2 * cb, "fine slab boundary must be twice the coarse one"
+            if r < world - 1:
+                assert ze % 2 == 0
+        if level < rep:
+            assert prev_end == Z
+        dims //= 2
+
+
+def test_partition_world1_and_small_grids_are_unpartitioned(gs):
+    for n, world in ((31, 1), (7, 8)):
+        zb, ze, rep = gs.partition(gs.make_params(n), world, 0, 0)
+        assert (zb, ze, rep) == (0, n + 2, 0)

@@ -1,0 +1,203 @@
+"""GPU suite: the CUDA backend, called through the C ABI, against the CPU oracle on the same
+inputs, against the golden vectors generated from the reference, and — at BASELINE.json's
+full sizes — through size-independent properties.
+
+Bars (BASELINE.json north_star): linear mode is BIT-EXACT (non-contracted, reference-ordered
+arithmetic); modes with exp() agree to <= 1e-12 relative (CUDA exp vs glibc exp, <= 1 ulp
+each); every residual norm agrees to <= 1e-12 relative with a compensated sum over the
+oracle's residual field."""
+import numpy as np
+import pytest
+
+from backends import F, NEWTONV, R, RESTV, V, CudaBackend, OracleBackend, operator_script
+from cases import BIG_CASES, OPERATOR_CASES, SOLVE_CASES, digest, rel_err, seeded_field
+
+pytestmark = pytest.mark.gpu
+
+FIELD_TOL = 1e-12   # relative (max-norm) tolerance for modes 1 and 2; mode 0 must be bitwise
+NORM_TOL = 1e-12
+
+
+def check_field(name, a, b, mode, exact_ok=True):
+    if mode == 0 and exact_ok:
+        assert np.array_equal(a + 0.0, b + 0.0), f"{name}: linear-mode field not bit-identical (max rel {rel_err(a, b):.3e})"
+    else:
+        assert rel_err(a, b) <= FIELD_TOL, f"{name}: rel err {rel_err(a, b):.3e}"
+
+
+def check_norm(name, a, b):
+    assert abs(a - b) <= NORM_TOL * max(abs(b), 1e-300) or a == b, f"{name}: {a!r} vs {b!r}"
+
+
+@pytest.mark.parametrize("kernels", [0, 1])
+@pytest.mark.parametrize("name", sorted(OPERATOR_CASES))
+def test_operators_match_oracle(name, kernels, gs, oracle_mod, golden, golden_fields):
+    kw = OPERATOR_CASES[name]
+    mode = kw["mode"]
+    dev = CudaBackend(gs, kernels=kernels, maxiter=1, **kw)
+    ref = OracleBackend("port", maxiter=1, **kw)
+    got, want = operator_script(dev, mode), operator_script(ref, mode)
+    assert set(got) == set(want)
+    for k in want:
+        if isinstance(want[k], float):
+            check_norm(k, got[k], want[k])
+        else:
+            # the tuned Newton smoother reads a precomputed coefficient: one rounding apart
+            check_field(k, got[k], want[k], mode)
+            if mode == 0:
+                assert digest(got[k]) == golden["operators"][name]["outputs"][k], k
+    dev.close()
+    ref.close()
+
+
+@pytest.mark.parametrize("kernels,graph", [(0, 0), (1, 0), (1, 1)])
+@pytest.mark.parametrize("name", sorted(SOLVE_CASES))
+def test_solves_match_oracle_and_golden(name, kernels, graph, gs, oracle_mod, golden):
+    kw, g = SOLVE_CASES[name], golden["solve"][name]
+    mode = kw["mode"]
+    dev = CudaBackend(gs, kernels=kernels, graph=graph, **kw)
+    ref = OracleBackend("port", **kw)
+    assert dev.num_levels == ref.num_levels == g["num_levels"]
+    for l in range(dev.num_levels):
+        assert dev.level_info(l) == ref.level_info(l)
+    f_dev, f_ref = dev.get(0, F), ref.get(0, F)
+    check_field("rhs", f_dev, f_ref, mode)
+    info = dev.solve()
+    hist = dev.history()
+    if mode == 2:
+        norms, inner = ref.newton_solve()
+        assert info.inner_cycles == inner == g["inner_cycles"], "inner V-cycle counts (early exit) differ"
+        sol_dev, sol_ref = dev.get(0, NEWTONV), ref.get(0, NEWTONV)
+    else:
+        norms = ref.solve()
+        sol_dev, sol_ref = dev.get(0, V), ref.get(0, V)
+    assert info.iterations == len(norms) - 1 == len(g["norms"]) - 1, "number of cycles run differs"
+    assert len(hist) == len(norms)
+    r0 = norms[0] if norms[0] > 0 else 1.0
+    for i, (a, b) in enumerate(zip(hist, norms)):
+        if mode == 0:
+            check_norm(f"norm[{i}]", a, b)
+        else:
+            # with exp() ulps the late-cycle norm is a cancellation; 1e-12 holds while
+            # |r|/|r0| >~ 1e-3, beyond that the floor is |d|r||/|r0|
+            assert abs(a - b) <= NORM_TOL * abs(b) or abs(a - b) <= 1e-13 * r0, (i, a, b)
+    check_field("solution", sol_dev, sol_ref, mode)
+    if mode == 0:
+        assert digest(sol_dev) == g["solution_digest"], "not bit-identical to the reference's field"
+    dev.close()
+    ref.close()
+
+
+def test_final_norm_matches_compensated_sum(gs, oracle_mod):
+    kw = dict(n=63, mode=0, pre=2, post=2, maxiter=2, tol=1e-30)
+    dev, ref = CudaBackend(gs, **kw), OracleBackend("port", **kw)
+    dev.solve()
+    ref.solve()
+    check_norm("final", dev.history()[-1], ref.norm_exact(0, R))
+    n = dev.residual(0)  # stores r
+    assert np.array_equal(dev.get(0, R), ref.get(0, R))
+    check_norm("residual()", n, ref.norm_exact(0, R))
+
+
+@pytest.mark.parametrize("name", sorted(BIG_CASES))
+def test_big_cases_against_golden(name, gs, golden):
+    """127^3 configs incl. the shipped example (Newton V(3,3)): golden norms from the reference"""
+    kw, g = BIG_CASES[name], golden["solve"][name]
+    dev = CudaBackend(gs, **kw)
+    info = dev.solve()
+    hist = dev.history()
+    want = [float.fromhex(x) for x in g["norms"]]
+    assert info.iterations == len(want) - 1
+    for i, (a, b) in enumerate(zip(hist, want)):
+        assert abs(a - b) <= 1e-11 * abs(b) or abs(a - b) <= 1e-13 * want[0], (i, a, b)
+    if kw["mode"] == 2:
+        assert info.inner_cycles == g["inner_cycles"]
+        sol = dev.get(0, NEWTONV)
+    else:
+        sol = dev.get(0, V)
+    z, y, x = sol.shape
+    centre = float.fromhex(g["centre"])
+    assert abs(sol[z // 2, y // 2, x // 2] - centre) <= FIELD_TOL * abs(centre)
+    if kw["mode"] == 0:
+        assert digest(sol) == g["solution_digest"]
+    dev.close()
+
+
+def test_shipped_config_through_the_driver_binary(gs, golden):
+    """GpuSolve-cuda <conf> prints the reference's stdout lines (src/cpu/NewtonSolver.cpp:16,27)"""
+    import os
+    import re
+    import subprocess
+    from cases import GOLDEN_DIR
+    r = subprocess.run([gs.EXE, os.path.join(GOLDEN_DIR, "data-2nd_order.conf")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    out = r.stdout.splitlines()
+    assert out[0].startswith('Using config file "') and out[1] == "Solving newton problem"
+    assert out[2] == "Inital newton residual: 281.289"
+    its = [re.fullmatch(r"newton iter: (\d+) residual: (\S+) Took (\d+)ms", l) for l in out[3:]]
+    assert all(its) and [m.group(2) for m in its] == ["12.3816", "0.527004", "0.0222718", "0.00093763"]
+
+
+def test_get_set_roundtrip_and_layouts(gs):
+    dev = CudaBackend(gs, n=(5, 7, 6), mode=1)
+    a = seeded_field(dev.shape(0), 7, interior_only=False)
+    dev.set(0, RESTV, a)
+    assert np.array_equal(dev.get(0, RESTV), a)
+    zf = dev.get_zfastest(0, RESTV)          # [x, y, z] like the reference's Vector3
+    assert np.array_equal(zf, a.transpose(2, 1, 0))
+    with pytest.raises(gs.GpuSolveError):
+        dev.get(0, NEWTONV)                  # not allocated in mode 1
+    with pytest.raises(gs.GpuSolveError):
+        dev.get(9, V)
+    dev.close()
+
+
+def test_dump_format_matches_vector3_dump(gs, tmp_path):
+    dev = CudaBackend(gs, n=3, mode=0)
+    dev.vcycle()
+    path = tmp_path / "v.txt"
+    dev.dump(0, V, path)
+    lines = path.read_text().splitlines()
+    assert lines[0] == "5 5 5" and len(lines) == 1 + 125
+    v = dev.get(0, V)
+    x, y, z, val = lines[1 + 2 * 25 + 2 * 5 + 2].split()  # x outer, z inner (src/cpu/Vector3.cpp:67-75)
+    assert (x, y, z) == ("2", "2", "2") and float(val) == pytest.approx(v[2, 2, 2], rel=1e-5)
+    dev.close()
+
+
+def test_smoother_is_linear_in_mode0(gs):
+    """S(a*v1 + v2; a*f1 + f2) == a*S(v1; f1) + S(v2; f2) up to rounding, any size"""
+    outs = []
+    shape = None
+    for sv, sf in ((11, 12), (13, 14)):
+        dev = CudaBackend(gs, n=(40, 33, 21), mode=0)
+        shape = dev.shape(0)
+        dev.set(0, V, seeded_field(shape, sv))
+        dev.set(0, F, seeded_field(shape, sf, scale=1.0))
+        dev.smooth(0, 3)
+        outs.append(dev.get(0, V))
+        dev.close()
+    dev = CudaBackend(gs, n=(40, 33, 21), mode=0)
+    dev.set(0, V, 2.0 * seeded_field(shape, 11) + seeded_field(shape, 13))
+    dev.set(0, F, 2.0 * seeded_field(shape, 12, scale=1.0) + seeded_field(shape, 14, scale=1.0))
+    dev.smooth(0, 3)
+    assert rel_err(dev.get(0, V), 2.0 * outs[0] + outs[1]) < 1e-13
+    dev.close()
+
+
+def test_full_size_513_properties(gs):
+    """n=511 (arrays 513^3), the benchmark grid: tuned == simple kernels bit for bit after a V(2,2)
+    cycle, residual norms match the reference's printed 6 digits (8328.23 -> 2840.32 ->
+    849.574), and the CUDA-graph path equals the plain-launch path."""
+    kw = dict(n=511, mode=0, pre=2, post=2, maxiter=2, tol=1e-30)
+    a = CudaBackend(gs, kernels=1, graph=1, **kw)
+    ia = a.solve()
+    ha = a.history()
+    assert [f"{x:.6g}" for x in ha] == ["8328.23", "2840.32", "849.574"]
+    va = digest(a.get(0, V))
+    a.close()
+    b = CudaBackend(gs, kernels=0, graph=0, **kw)
+    b.solve()
+    assert b.history() == ha and ia.iterations == 2
+    assert digest(b.get(0, V)) == va
+    b.close()
