@@ -744,7 +744,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->cx.stream = h->stream;
     h->cx.launches = &h->launches;
     h->cx.sm_count = prop.multiProcessorCount;
-    h->cx.tune.smooth_variant = 2;
+    h->cx.tune.smooth_variant = 22;
     h->cx.tune.zchunk = 64;
     h->cx.tune.fast_min_n = 48;
     if (const char* ev = getenv("GPUSOLVE_SMOOTH_VARIANT")) h->cx.tune.smooth_variant = atoi(ev);
@@ -767,8 +767,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
             return code;
         }
     }
+    // the zero fills above ran on the legacy stream, which the handle's non-blocking stream does not wait for
+    e = cudaDeviceSynchronize();
     // analytic right-hand side on level 0, src/cpu/CpuGridData.cpp:45-78
-    e = ks_init_rhs(h->cx, h->lev[0].g, p->mode, h->p.h, p->gamma, h->lev[0].f);
+    if (e == cudaSuccess) e = ks_init_rhs(h->cx, h->lev[0].g, p->mode, h->p.h, p->gamma, h->lev[0].f);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     if (e != cudaSuccess) {
         gs_destroy(h);
@@ -923,8 +925,9 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
             int rc = gs_comm_gather_to_host(h->comm, *slot, g.plane, g.pitch, g.z0, level, dense, X, Y, Z, h->stream);
             if (rc != 0) return fail(GS_ECOMM, "field gather failed: %s", gs_comm_error(h->comm));
         } else {
-            CU(cudaMemcpy2D(dense, X * sizeof(double), *slot + GS_XOFF, g.pitch * sizeof(double), X * sizeof(double), Y * Z,
-                            cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy2DAsync(dense, X * sizeof(double), *slot + GS_XOFF, g.pitch * sizeof(double), X * sizeof(double), Y * Z,
+                                 cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
         }
         if (layout == GS_LAYOUT_Z_FASTEST)
             for (size_t x = 0; x < X; x++)
@@ -935,9 +938,12 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
         const double* src = dense + X * Y * (size_t)g.z0;
         std::vector<double*> dst = {*slot};
         if (field == GS_FIELD_V) dst.push_back(L.vtmp);  // keep the halo of both ping-pong buffers identical
+        // on the handle's own (non-blocking) stream: a legacy-stream cudaMemcpy2D from pageable memory returns
+        // once the data is staged, and the DMA would race with the next kernel queued on h->stream
         for (double* d : dst)
-            CU(cudaMemcpy2D(d + GS_XOFF, g.pitch * sizeof(double), src, X * sizeof(double), X * sizeof(double),
-                            Y * (size_t)g.nzl, cudaMemcpyHostToDevice));
+            CU(cudaMemcpy2DAsync(d + GS_XOFF, g.pitch * sizeof(double), src, X * sizeof(double), X * sizeof(double),
+                                 Y * (size_t)g.nzl, cudaMemcpyHostToDevice, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
         if (field == GS_FIELD_NEWTONV) L.coef_valid = false;
         if (field == GS_FIELD_NEWTONF) h->newton_begun = true;
     }

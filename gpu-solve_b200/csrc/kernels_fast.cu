@@ -144,7 +144,10 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
 
 template <int TX, int TY, int NSTAGE>
 struct TmaCfg {
-    static constexpr int VW = TX + 2, VH = TY + 2;               // v box with its rim
+    // v box with its rim.  A TMA box must START on a 16-byte boundary in global memory (measured on this
+    // B200/driver: an 8-byte-aligned start raises "illegal instruction", tools/tma_probe.cu), and x0 sits on a
+    // 128-byte boundary, so the box takes two columns on either side instead of one.
+    static constexpr int VW = TX + 4, VH = TY + 2;
     static constexpr int V_BYTES = VW * VH * 8;
     static constexpr int V_STRIDE = (V_BYTES + 127) / 128 * 128;  // every TMA destination 128-B aligned
     static constexpr int F_BYTES = TX * TY * 8;
@@ -189,7 +192,7 @@ __global__ void __launch_bounds__(TX* TY + 32) smooth_tma(const __grid_constant_
                 const bool has_f = q >= 1 && q <= nz;
                 mbar_expect_tx(&full[s], Cfg::V_BYTES + (has_f ? Cfg::F_BYTES : 0));
                 unsigned char* st = smem + s * Cfg::STAGE;
-                tma_load_3d(st, &map_v, &full[s], GS_XOFF + x0 - 1, y0 - 1, z0 - 1 + q);
+                tma_load_3d(st, &map_v, &full[s], GS_XOFF + x0 - 2, y0 - 1, z0 - 1 + q);
                 if (has_f) tma_load_3d(st + Cfg::V_STRIDE, &map_f, &full[s], GS_XOFF + x0, y0, z0 - 1 + q);
             }
         }
@@ -201,7 +204,7 @@ __global__ void __launch_bounds__(TX* TY + 32) smooth_tma(const __grid_constant_
     const int x = x0 + tx, y = y0 + ty;
     const bool live = x <= p.g.nx && y <= p.g.ny;
     const int lane0 = (tid & 31) == 0;
-    const int ctr = (ty + 1) * Cfg::VW + tx + 1;  // centre inside a v box
+    const int ctr = (ty + 1) * Cfg::VW + tx + 2;  // centre inside a v box
     i64 c = gs_idx(p.g, min(x, p.g.nx), min(y, p.g.ny), z0);
 
     auto vbox = [&](int q) { return (const double*)(smem + (q % NSTAGE) * Cfg::STAGE); };

@@ -87,6 +87,9 @@ def operator_script(b, mode):
     out["smooth1_v"] = b.get(0, V)
     b.smooth(0, 2)
     out["smooth3_v"] = b.get(0, V)
+    # the fused CUDA sweeps never store r (the reference's jacobi leaves the residual of the last-but-one
+    # iterate there, which nothing reads: CpuSolver::vcycle recomputes it at :93); define r before using it
+    out["res3_norm"] = b.residual(0)
     b.restrict(0, R, F)
     out["restrict_r_f1"] = b.get(1, F)
     b.restrict(0, V, V)
