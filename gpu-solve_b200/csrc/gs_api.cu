@@ -326,7 +326,11 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     OpScope t(h, GS_OP_RESIDUAL, level);
-    CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
+    bool handled = false;
+    if (h->opt_kernels && h->canonical)
+        CU(kf_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled));
+    if (!handled)
+        CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
     return GS_OK;
 }
 
@@ -369,6 +373,13 @@ int do_restrict_residual(gs_handle* h, int level)
     }
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
+    if (h->opt_kernels && h->canonical && !partitioned(h, level)) {
+        // fused: the residual never goes to memory (kernels_transfer.cu)
+        Level& C = h->lev[level + 1];
+        bool handled = false;
+        CU(kt_resid_restrict(h->cx, km, L.pow2, L.g, C.g, C.ib, C.ie, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
+        if (handled) return GS_OK;
+    }
     CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
     GS(do_restrict(h, level, L.r, h->lev[level + 1].f, nullptr));
     return GS_OK;
@@ -396,7 +407,9 @@ int do_prolong_correct(gs_handle* h, int level)
     // an odd number of sweeps per cycle would leave v/vtmp swapped; writing the corrected
     // field out of place in that case keeps the buffer parity (and the CUDA graph) fixed
     const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
-    CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
+    bool handled = false;
+    if (h->opt_kernels) CU(kt_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, &handled));
+    if (!handled) CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
     if (flip) std::swap(F.v, F.vtmp);
     GS(exchange_halo(h, level, F.v, 1));
     return GS_OK;
@@ -443,6 +456,7 @@ uint64_t parity_key(const gs_handle* h)
     key |= (uint64_t)h->opt_kernels << 40;
     key |= (uint64_t)(h->cx.tune.smooth_variant & 0x3f) << 32;
     key ^= (uint64_t)(h->cx.tune.zchunk & 0xfff) << 20;
+    key ^= (uint64_t)(h->cx.tune.rr_variant & 1) << 19;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     return key;
@@ -750,7 +764,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* ev = getenv("GPUSOLVE_SMOOTH_VARIANT")) h->cx.tune.smooth_variant = atoi(ev);
     if (const char* ev = getenv("GPUSOLVE_ZCHUNK")) h->cx.tune.zchunk = std::max(1, atoi(ev));
     if (const char* ev = getenv("GPUSOLVE_FAST_MIN_N")) h->cx.tune.fast_min_n = atoi(ev);
+    h->cx.tune.rr_variant = 0;
+    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = atoi(ev) != 0;
     e = kf_prepare();
+    if (e == cudaSuccess) e = kt_prepare();
     if (e != cudaSuccess) {
         gs_destroy(h);
         return fail(GS_ECUDA, "kernel setup failed: %s", cudaGetErrorString(e));
@@ -1187,6 +1204,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
+    else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
     else return fail(GS_EINVAL, "unknown option \"%s\"", name);
     return GS_OK;
 }

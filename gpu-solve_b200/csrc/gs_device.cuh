@@ -1,0 +1,184 @@
+// gs_device.cuh — device-side building blocks shared by kernels_simple.cu and the tuned
+// kernels: the per-point arithmetic (one definition, so every kernel variant produces the same
+// bits), the deterministic sum-of-squares reduction, and the mbarrier / TMA PTX wrappers.
+//
+// Arithmetic contract (DESIGN.md "Parity"): the library is compiled with -fmad=false, so every
+// expression below is evaluated with separate IEEE fp64 multiplies and adds in the order written,
+// which is the order of the reference (cited per function, paths relative to the reference root).
+#pragma once
+#include <cuda.h>
+
+#include "gs_internal.h"
+
+// ---- host helpers shared by the tuned translation units (kernels_fast.cu) ----
+// TMA descriptor of a level array viewed as [nzl][Y][pitch] doubles with a bw x bh x 1 box (cached)
+bool gs_tensor_map(const double* base, const Geom& g, int bw, int bh, CUtensorMap* out);
+// planes per CTA of a z-marching kernel: long chunks (each re-reads its rim planes), but short
+// enough that small levels still put several CTAs on every SM
+int gs_pick_zchunk(const LaunchCtx& cx, int tiles, int planes, int max_chunk);
+
+// ---------------------------------------------------------------------------------
+// point arithmetic
+// ---------------------------------------------------------------------------------
+// s = sum_i c_i v(p+o_i) (already accumulated, i ascending: src/cpu/CpuSolver.cpp:56-60)
+// -> r = f - (s/(h*h) + NL), and the Jacobi denominator (modes 1..3)
+// src/cpu/CpuSolver.cpp:61-74 (residual) and :161-171 (denominator)
+template <int KM, bool POW2>
+__device__ __forceinline__ double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
+{
+    s = POW2 ? s * k.inv_hh : s / k.hh;
+    den = 0.0;
+    if (KM == KM_NONLINEAR) {
+        double ex = exp(vc);
+        double nl = (k.gamma * vc) * ex;
+        s += nl;
+        den = k.preFac + (k.gamma * (1 + vc)) * ex;
+    } else if (KM == KM_NEWTON_EXP) {
+        double ex = exp(aux);
+        double g1 = k.gamma * (1 + aux);
+        s += (g1 * vc) * ex;
+        den = k.preFac + g1 * ex;
+    } else if (KM == KM_NEWTON_COEF) {
+        // aux = (gamma*(1+nv))*exp(nv) precomputed once per Newton step (ks_newton_coef);
+        // (g1*ex)*v instead of (g1*v)*ex: one rounding apart, inside the exp() tolerance
+        s += aux * vc;
+        den = k.preFac + aux;
+    }
+    return fc - s;
+}
+
+template <int KM>
+__device__ __forceinline__ double jacobi_update(double vc, double r, double den, const PointK& k)
+{
+    // src/cpu/CpuSolver.cpp:158 resp. :164,:171
+    if (KM == KM_LINEAR) return vc + k.omega * (k.alpha * r);
+    return vc + k.omega * (r / den);
+}
+
+// canonical tap order C,+x,-x,+y,-y,+z,-z (config order of the axis-aligned stencil)
+__device__ __forceinline__ double canon_tap_sum(double C, double E, double W, double N, double S, double U, double D, const PointK& k)
+{
+    double s = 0.0;
+    s += k.c[0] * C;
+    s += k.c[1] * E;
+    s += k.c[2] * W;
+    s += k.c[3] * N;
+    s += k.c[4] * S;
+    s += k.c[5] * U;
+    s += k.c[6] * D;
+    return s;
+}
+
+template <int KM, bool POW2>
+__device__ __forceinline__ double canon_residual(double C, double E, double W, double N, double S, double U, double D, double fv,
+                                                 double aux, const PointK& k, double& den)
+{
+    return finish_residual<KM, POW2>(canon_tap_sum(C, E, W, N, S, U, D, k), C, fv, aux, k, den);
+}
+
+// ---------------------------------------------------------------------------------
+// deterministic sum of squares: CTA tree, then the last CTA to finish adds the per-CTA
+// partials in index order with the same tree (no floating-point atomics; the result does
+// not depend on which CTA happens to be last)
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// sum over the first NT threads (tid 0..NT-1, NT a multiple of 32) of the CTA; the other threads
+// of the CTA (e.g. a TMA producer warp) must not call it.  Uses named barrier 1.
+template <int NT>
+__device__ __forceinline__ double block_sum(double v, double* sh, int tid)
+{
+    v = warp_sum(v);
+    if ((tid & 31) == 0) sh[tid >> 5] = v;
+    asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+    double t = 0.0;
+    if (tid < 32) {
+        t = tid < NT / 32 ? sh[tid] : 0.0;
+        t = warp_sum(t);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+    return t;  // valid in thread 0
+}
+
+template <int NT>
+__device__ __forceinline__ void grid_sum_finish(double block_total, NormBuf nb, double* sh, int tid)
+{
+    const unsigned nblk = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned bid = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    __shared__ int last;
+    if (tid == 0) {
+        nb.partials[bid] = block_total;
+        __threadfence();
+        unsigned t = atomicAdd(nb.ticket, 1u);
+        last = (t == nblk - 1);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+    if (!last) return;
+    __threadfence();
+    double acc = 0.0;
+    for (unsigned i = tid; i < nblk; i += NT) acc += __ldcg(&nb.partials[i]);
+    double tot = block_sum<NT>(acc, sh, tid);
+    if (tid == 0) {
+        *nb.result = tot;
+        *nb.ticket = 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------
+// mbarrier / TMA (cp.async.bulk.tensor, SASS UTMALDG)
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.b32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+// 3-D tiled load of one box; the box must START on a 16-byte boundary in global memory
+// (tools/tma_probe.cu: an 8-byte-aligned start raises "illegal instruction" on B200)
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+// consumer-only barrier (named barrier 2) for kernels whose producer warp runs ahead
+template <int NT>
+__device__ __forceinline__ void consumer_sync()
+{
+    asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
+}

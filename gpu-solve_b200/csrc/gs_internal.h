@@ -63,6 +63,7 @@ struct Tune {
     int smooth_variant;  // 0 simple, 1x z-march through L1, 2x TMA-staged z-march (kernels_fast.cu)
     int zchunk;          // planes per CTA of the z-marching kernels
     int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
+    int rr_variant;      // tile of the fused residual+restriction kernel: 0 = 32x8 coarse columns, 1 = 32x4
 };
 
 struct LaunchCtx {
@@ -106,3 +107,13 @@ bool kf_available();
 cudaError_t kf_prepare();
 cudaError_t kf_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
                       const double* vin, double* vout, const double* f, const double* aux, bool* handled);
+// r = f - A(v) (stored if r != nullptr) and sum of squares -> cx.norm.result
+cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                        const double* v, const double* f, const double* aux, double* r, bool* handled);
+
+// ---- kernels_transfer.cu: tuned grid-transfer kernels (canonical stencil) ----
+cudaError_t kt_prepare();
+cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
+                               double* vout, const double* coarse, bool* handled);
+cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, bool pow2, const Geom& gf, const Geom& gc, int zcb, int zce,
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled);

@@ -9,7 +9,7 @@
 // (cited per function, paths relative to the reference root).  Linear-mode
 // fields are therefore bit-identical to GpuSolve-cpu; modes with exp() differ by
 // CUDA-vs-glibc exp rounding only.
-#include "gs_internal.h"
+#include "gs_device.cuh"
 
 namespace {
 
@@ -35,40 +35,6 @@ __device__ __forceinline__ double tap_sum(const double* __restrict__ a, i64 c, c
     return s;
 }
 
-// s -> r = f - (s/(h*h) + NL), and the Jacobi denominator (modes 1..3)
-// src/cpu/CpuSolver.cpp:61-74 (residual) and :161-171 (denominator)
-template <int KM, bool POW2>
-__device__ __forceinline__ double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
-{
-    s = POW2 ? s * k.inv_hh : s / k.hh;
-    den = 0.0;
-    if (KM == KM_NONLINEAR) {
-        double ex = exp(vc);
-        double nl = (k.gamma * vc) * ex;
-        s += nl;
-        den = k.preFac + (k.gamma * (1 + vc)) * ex;
-    } else if (KM == KM_NEWTON_EXP) {
-        double ex = exp(aux);
-        double g1 = k.gamma * (1 + aux);
-        s += (g1 * vc) * ex;
-        den = k.preFac + g1 * ex;
-    } else if (KM == KM_NEWTON_COEF) {
-        // aux = (gamma*(1+nv))*exp(nv) precomputed once per Newton step (ks_newton_coef);
-        // (g1*ex)*v instead of (g1*v)*ex: one rounding apart, inside the exp() tolerance
-        s += aux * vc;
-        den = k.preFac + aux;
-    }
-    return fc - s;
-}
-
-template <int KM>
-__device__ __forceinline__ double jacobi_update(double vc, double r, double den, const PointK& k)
-{
-    // src/cpu/CpuSolver.cpp:158 resp. :164,:171
-    if (KM == KM_LINEAR) return vc + k.omega * (k.alpha * r);
-    return vc + k.omega * (r / den);
-}
-
 template <int KM, bool POW2>
 __global__ void __launch_bounds__(BX* BY) smooth_simple(SmoothP p)
 {
@@ -83,56 +49,6 @@ __global__ void __launch_bounds__(BX* BY) smooth_simple(SmoothP p)
     double den;
     const double r = finish_residual<KM, POW2>(s, vc, p.f[c], aux, p.k, den);
     p.vout[c] = jacobi_update<KM>(vc, r, den, p.k);
-}
-
-// ---- deterministic sum of squares: CTA tree, then the last CTA to finish adds
-// the per-CTA partials in index order with the same tree (no fp atomics) ----
-__device__ __forceinline__ double warp_sum(double v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-    return v;
-}
-
-template <int NT>
-__device__ __forceinline__ double block_sum(double v, double* sh)
-{
-    const int tid = threadIdx.x + threadIdx.y * blockDim.x;
-    v = warp_sum(v);
-    if ((tid & 31) == 0) sh[tid >> 5] = v;
-    __syncthreads();
-    double t = 0.0;
-    if (tid < 32) {
-        t = tid < NT / 32 ? sh[tid] : 0.0;
-        t = warp_sum(t);
-    }
-    __syncthreads();
-    return t;  // valid in thread 0
-}
-
-template <int NT>
-__device__ __forceinline__ void grid_sum_finish(double block_total, NormBuf nb, double* sh)
-{
-    const int tid = threadIdx.x + threadIdx.y * blockDim.x;
-    const unsigned nblk = gridDim.x * gridDim.y * gridDim.z;
-    const unsigned bid = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-    __shared__ bool last;
-    if (tid == 0) {
-        nb.partials[bid] = block_total;
-        __threadfence();
-        unsigned t = atomicAdd(nb.ticket, 1u);
-        last = (t == nblk - 1);
-    }
-    __syncthreads();
-    if (!last) return;
-    __threadfence();
-    double acc = 0.0;
-    for (unsigned i = tid; i < nblk; i += NT) acc += __ldcg(&nb.partials[i]);
-    double tot = block_sum<NT>(acc, sh);
-    if (tid == 0) {
-        *nb.result = tot;
-        *nb.ticket = 0u;
-    }
 }
 
 struct ResidP {
@@ -166,8 +82,9 @@ __global__ void __launch_bounds__(BX* BY) residual_simple(ResidP p)
         if (p.r) p.r[c] = r;
         sq = r * r;
     }
-    double tot = block_sum<BX * BY>(sq, sh);
-    grid_sum_finish<BX * BY>(tot, p.nb, sh);
+    const int tid = threadIdx.x + threadIdx.y * BX;
+    double tot = block_sum<BX * BY>(sq, sh, tid);
+    grid_sum_finish<BX * BY>(tot, p.nb, sh, tid);
 }
 
 struct RestrictP {
@@ -299,8 +216,9 @@ __global__ void __launch_bounds__(BX* BY) newton_F_simple(NewtonFP p)
         p.f[c] = fv;
         sq = fv * fv;
     }
-    double tot = block_sum<BX * BY>(sq, sh);
-    grid_sum_finish<BX * BY>(tot, p.nb, sh);
+    const int tid = threadIdx.x + threadIdx.y * BX;
+    double tot = block_sum<BX * BY>(sq, sh, tid);
+    grid_sum_finish<BX * BY>(tot, p.nb, sh, tid);
 }
 
 __global__ void __launch_bounds__(BX* BY) newton_coef_simple(Geom g, int zb, double gamma, const double* __restrict__ nv,

@@ -58,6 +58,12 @@ OPERATOR_CASES = {
     "op_nl_ragged": dict(n=(10, 7, 13), mode=1),
     "op_nt17": dict(n=17, mode=2),
     "op_nt_ragged": dict(n=(10, 7, 13), mode=2),
+    # large enough for the tuned kernels (TMA z-march smoother/residual, fused residual+restriction,
+    # paired prolongation); odd, even and ragged extents exercise their edge masks
+    "op_lin_mid": dict(n=(70, 53, 41), mode=0),
+    "op_lin_mid_even": dict(n=(64, 66, 34), mode=0),
+    "op_nl_mid": dict(n=(67, 50, 38), mode=1),
+    "op_nt_mid": dict(n=(63, 49, 35), mode=2),
 }
 
 

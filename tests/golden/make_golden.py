@@ -59,7 +59,8 @@ def operator_case(name, kw, arrays):
             rec["outputs"][k] = v.hex()
         else:
             rec["outputs"][k] = digest(v)
-            arrays[name + "/" + k] = v
+            if v.size <= 24 ** 3:
+                arrays[name + "/" + k] = v
     b.close()
     return rec
 

@@ -52,7 +52,8 @@ def test_port_matches_golden_operators(name, oracle_mod, golden, golden_fields):
         if isinstance(v, float):
             assert _close(v, float.fromhex(g["outputs"][k])), k
         else:
-            assert np.array_equal(v, golden_fields[name + "/" + k]), k
+            if name + "/" + k in golden_fields:
+                assert np.array_equal(v, golden_fields[name + "/" + k]), k
             assert digest(v) == g["outputs"][k], k
     b.close()
 

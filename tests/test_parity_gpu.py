@@ -198,6 +198,9 @@ def test_full_size_513_properties(gs):
     a.close()
     b = CudaBackend(gs, kernels=0, graph=0, **kw)
     b.solve()
-    assert b.history() == ha and ia.iterations == 2
+    # fields are bit-identical; the norms differ only by the summation tree of the two residual kernels
+    assert ia.iterations == 2 and len(b.history()) == len(ha)
+    for x, y in zip(b.history(), ha):
+        check_norm("simple vs tuned norm", x, y)
     assert digest(b.get(0, V)) == va
     b.close()
