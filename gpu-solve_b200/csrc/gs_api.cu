@@ -61,6 +61,7 @@ struct Level {
     size_t count;     // doubles per array
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
     bool coef_valid;
+    bool pre_valid;   // vtmp == one Jacobi sweep of v for the current f/aux (written by the fused sweep+norm kernel)
 };
 
 struct EventPair {
@@ -80,9 +81,10 @@ struct gs_handle {
     LaunchCtx cx;
     double* h_norm;  // pinned
     uint64_t launches;
-    int opt_kernels, opt_graph, opt_timing;
+    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
+    std::map<uint64_t, bool> graphs_pre_valid;     // lev[0].pre_valid after a replay of each graph
     std::vector<double> history;
     std::vector<EventPair> ev_used;
     std::vector<cudaEvent_t> ev_free;
@@ -296,6 +298,13 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     const int km = smoother_km(h);
     if (km == KM_NEWTON_COEF && iters > 0) GS(ensure_coef(h, level));
     OpScope t(h, GS_OP_SMOOTH, level);
+    if (L.pre_valid && iters > 0) {
+        // the first sweep was already produced together with the last residual norm (do_norm_residual)
+        L.pre_valid = false;
+        std::swap(L.v, L.vtmp);
+        GS(exchange_halo(h, level, L.v, 1));
+        iters--;
+    }
     for (uint64_t it = 0; it < iters; it++) {
         bool handled = false;
         if (h->opt_kernels && h->canonical)
@@ -332,6 +341,26 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     if (!handled)
         CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
     return GS_OK;
+}
+
+// level-0 residual norm when nothing needs r itself (end of a V-cycle, start of a solve).  The next thing that
+// happens to level 0 is then a pre-smoothing sweep, which starts from exactly this residual, so the tuned path
+// produces that sweep in the same pass (vtmp = S(v), v untouched, Level::pre_valid) instead of reading v and f twice.
+int do_norm_residual(gs_handle* h)
+{
+    Level& L = h->lev[0];
+    const int km = smoother_km(h);
+    if (h->opt_fuse_norm && h->opt_kernels && h->canonical && h->p.pre > 0 && !L.pre_valid) {
+        if (km == KM_NEWTON_COEF) GS(ensure_coef(h, 0));
+        OpScope t(h, GS_OP_RESIDUAL, 0);
+        bool handled = false;
+        CU(kf_smooth_norm(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, smoother_aux(h, 0, km), &handled));
+        if (handled) {
+            L.pre_valid = true;
+            return GS_OK;
+        }
+    }
+    return do_residual(h, 0, false, L.ib, L.ie);
 }
 
 // restrict a level array onto the next level (src/cpu/CpuSolver.cpp:211-238);
@@ -401,6 +430,7 @@ int do_prolong_correct(gs_handle* h, int level)
     Level& F = h->lev[level];
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_PROLONG, level);
+    F.pre_valid = false;
     if (h->p.mode == GS_MODE_NONLINEAR) {
         CU(ks_axpy(h->cx, C.g, 0, C.g.nzl, C.v, C.restV, -1));
     }
@@ -417,6 +447,7 @@ int do_prolong_correct(gs_handle* h, int level)
 
 int zero_field(gs_handle* h, Level& L, double* a)
 {
+    L.pre_valid = false;
     OpScope t(h, GS_OP_OTHER, (int)(&L - h->lev.data()));
     CU(cudaMemsetAsync(a, 0, L.count * sizeof(double), h->stream));
     return GS_OK;
@@ -442,7 +473,7 @@ int enqueue_vcycle(gs_handle* h)
         GS(do_prolong_correct(h, i - 1));
         GS(do_smooth(h, i - 1, h->p.post));
     }
-    GS(do_residual(h, 0, false, h->lev[0].ib, h->lev[0].ie));
+    GS(do_norm_residual(h));
     GS(norm_to_host(h, 0));
     return GS_OK;
 }
@@ -457,6 +488,8 @@ uint64_t parity_key(const gs_handle* h)
     key |= (uint64_t)(h->cx.tune.smooth_variant & 0x3f) << 32;
     key ^= (uint64_t)(h->cx.tune.zchunk & 0xfff) << 20;
     key ^= (uint64_t)(h->cx.tune.rr_variant & 1) << 19;
+    key ^= (uint64_t)(h->lev[0].pre_valid ? 1 : 0) << 18;
+    key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     return key;
@@ -480,6 +513,7 @@ int run_vcycle(gs_handle* h, double* norm)
                 t0.push_back(L.vtmp);
             }
             const uint64_t l0 = h->launches;
+            const bool pre0 = h->lev[0].pre_valid;
             cudaGraph_t g = nullptr;
             CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             int rc = enqueue_vcycle(h);
@@ -491,6 +525,8 @@ int run_vcycle(gs_handle* h, double* norm)
             }
             uint64_t per_cycle = h->launches - l0;
             h->launches = l0;
+            const bool pre1 = h->lev[0].pre_valid;
+            h->lev[0].pre_valid = pre0;
             if (rc != GS_OK) {
                 if (g) cudaGraphDestroy(g);
                 return rc;
@@ -501,9 +537,11 @@ int run_vcycle(gs_handle* h, double* norm)
             cudaGraphDestroy(g);
             it = h->graphs.emplace(key, ex).first;
             h->graphs_launches[key] = per_cycle;
+            h->graphs_pre_valid[key] = pre1;
         }
         CU(cudaGraphLaunch(it->second, h->stream));
         h->launches += h->graphs_launches[key];
+        h->lev[0].pre_valid = h->graphs_pre_valid[key];
         // host-side view of the buffer parity after the cycle
         const int last = (int)h->lev.size() - 1;
         const bool odd = ((h->p.pre + h->p.post) & 1) != 0;
@@ -538,7 +576,10 @@ int solve_mg(gs_handle* h, uint64_t maxiter, double tol, bool print, std::vector
              bool* converged)
 {
     double initial;
-    GS(residual_norm_sync(h, 0, true, &initial));
+    GS(do_norm_residual(h));
+    GS(norm_to_host(h, 0));
+    CU(cudaStreamSynchronize(h->stream));
+    initial = sqrt(*h->h_norm);
     if (print) std::cout << "Inital residual: " << initial << '\n';
     if (hist) hist->push_back(initial);
     *cycles = 0;
@@ -574,6 +615,7 @@ int newton_begin(gs_handle* h)
 int newton_compF(gs_handle* h, double* norm)
 {
     Level& L = h->lev[0];
+    L.pre_valid = false;  // f changes
     {
         OpScope t(h, GS_OP_RESIDUAL, 0);
         CU(ks_newton_F(h->cx, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.newtonV, h->newtonF, L.f));
@@ -604,6 +646,7 @@ int newton_find_error(gs_handle* h, uint64_t* inner)
         CU(ks_axpy(h->cx, L0.g, 0, L0.g.nzl, L0.newtonV, L0.v, +1));  // :106-107
     }
     L0.coef_valid = false;
+    L0.pre_valid = false;
     return GS_OK;
 }
 
@@ -666,6 +709,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_kernels = 1;
     h->opt_graph = 1;
     h->opt_timing = 0;
+    h->opt_fuse_norm = 1;
     h->comm = nullptr;
     h->h_norm = nullptr;
     memset(h->op_ms, 0, sizeof h->op_ms);
@@ -678,6 +722,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->canonical = canonical_offsets(*p);
     if (const char* e = getenv("GPUSOLVE_KERNELS")) h->opt_kernels = atoi(e) != 0;
     if (const char* e = getenv("GPUSOLVE_GRAPH")) h->opt_graph = atoi(e) != 0;
+    if (const char* e = getenv("GPUSOLVE_FUSE_NORM")) h->opt_fuse_norm = atoi(e) != 0;
 
     Partition part = make_partition(*p, world);
     h->replicated_from = part.replicated_from;
@@ -961,6 +1006,7 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
             CU(cudaMemcpy2DAsync(d + GS_XOFF, g.pitch * sizeof(double), src, X * sizeof(double), X * sizeof(double),
                                  Y * (size_t)g.nzl, cudaMemcpyHostToDevice, h->stream));
         CU(cudaStreamSynchronize(h->stream));
+        L.pre_valid = false;
         if (field == GS_FIELD_NEWTONV) L.coef_valid = false;
         if (field == GS_FIELD_NEWTONF) h->newton_begun = true;
     }
@@ -1200,6 +1246,10 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->opt_kernels = value != 0;
         for (auto& L : h->lev) L.coef_valid = false;
     } else if (n == "graph") h->opt_graph = value != 0;
+    else if (n == "fuse_norm") {
+        h->opt_fuse_norm = value != 0;
+        h->lev[0].pre_valid = false;
+    }
     else if (n == "timing") h->opt_timing = value != 0;
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);

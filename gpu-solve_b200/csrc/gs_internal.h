@@ -110,6 +110,9 @@ cudaError_t kf_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int
 // r = f - A(v) (stored if r != nullptr) and sum of squares -> cx.norm.result
 cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
                         const double* v, const double* f, const double* aux, double* r, bool* handled);
+// vout = sweep(vin) and sum of squares of the residual of vin -> cx.norm.result
+cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                           const double* vin, double* vout, const double* f, const double* aux, bool* handled);
 
 // ---- kernels_transfer.cu: tuned grid-transfer kernels (canonical stencil) ----
 cudaError_t kt_prepare();

@@ -86,7 +86,7 @@ bool kf_available() { return encode_fn() != nullptr; }
 
 namespace {
 
-enum { OP_SMOOTH = 0, OP_RESID = 1 };
+enum { OP_SMOOTH = 0, OP_RESID = 1, OP_SMOOTH_NORM = 2 };  // 2: the sweep's new iterate AND sum r^2 of the old one
 
 struct FastP {
     Geom g;
@@ -227,6 +227,13 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
         if (OP == OP_SMOOTH) {
             const double nv = point_update<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k);
             if (live) p.vout[c] = nv;
+        } else if (OP == OP_SMOOTH_NORM) {
+            double den;
+            const double r = canon_residual<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k, den);
+            if (live) {
+                p.vout[c] = jacobi_update<KM>(C, r, den, p.k);
+                sq += r * r;
+            }
         } else {
             double den;
             const double r = canon_residual<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k, den);
@@ -240,7 +247,7 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
         c += p.g.plane;
     }
     // the last plane (q = nz+1) was only read for its centre; nobody refills it
-    if (OP == OP_RESID) {
+    if (OP != OP_SMOOTH) {
         __shared__ double sh[32];
         const double tot = block_sum<Cfg::CONSUMERS>(sq, sh, tid);
         grid_sum_finish<Cfg::CONSUMERS>(tot, p.nb, sh, tid);
@@ -267,7 +274,7 @@ cudaError_t launch_tma(const LaunchCtx& cx, FastP p, bool* handled)
     p.zchunk = gs_pick_zchunk(cx, ((p.g.nx + TX - 1) / TX) * ((p.g.ny + TY - 1) / TY), p.ze - p.zb, p.zchunk);
     const int nzc = (p.ze - p.zb + p.zchunk - 1) / p.zchunk;
     dim3 grid((p.g.nx + TX - 1) / TX, (p.g.ny + TY - 1) / TY, nzc);
-    if (OP == OP_RESID && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;  // not handled
+    if (OP != OP_SMOOTH && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;  // not handled
     stencil_tma<KM, POW2, OP, TX, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
     *handled = true;
     return cudaGetLastError();
@@ -306,12 +313,12 @@ cudaError_t dispatch_smooth(const LaunchCtx& cx, const FastP& p, int variant, bo
     }
 }
 
-template <int KM, bool POW2>
+template <int KM, bool POW2, int OP>
 cudaError_t dispatch_resid(const LaunchCtx& cx, const FastP& p, bool* handled)
 {
     // wide tiles on big levels, the narrow tile where 128 columns would leave most of a CTA idle
-    if (p.g.nx >= 96) return launch_tma<KM, POW2, OP_RESID, 128, 4, 4>(cx, p, handled);
-    return launch_tma<KM, POW2, OP_RESID, 64, 4, 4>(cx, p, handled);
+    if (p.g.nx >= 96) return launch_tma<KM, POW2, OP, 128, 4, 4>(cx, p, handled);
+    return launch_tma<KM, POW2, OP, 64, 4, 4>(cx, p, handled);
 }
 
 // run `what` for every (mode, pow2) instantiation
@@ -361,7 +368,29 @@ cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
     p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
     if (v && p.zchunk > ze - zb) p.zchunk = ze - zb;
     cudaError_t e = cudaSuccess;
-#define CALL(KMV) e = pow2 ? dispatch_resid<KMV, true>(cx, p, handled) : dispatch_resid<KMV, false>(cx, p, handled)
+#define CALL(KMV) e = pow2 ? dispatch_resid<KMV, true, OP_RESID>(cx, p, handled) : dispatch_resid<KMV, false, OP_RESID>(cx, p, handled)
+    FOR_ALL_KM(CALL);
+#undef CALL
+    if (e == cudaSuccess && *handled && cx.launches) ++*cx.launches;
+    return e;
+}
+
+// vout = one Jacobi sweep of vin, and sum of squares of the residual of vin -> cx.norm.result: the residual the
+// V-cycle returns (src/cpu/CpuSolver.cpp:138) is the one the next cycle's first pre-smoothing sweep starts from (:88)
+cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                           const double* vin, double* vout, const double* f, const double* aux, bool* handled)
+{
+    *handled = false;
+    if (vin) {
+        if (ze <= zb) return cudaSuccess;
+        if (g.nx < cx.tune.fast_min_n || g.ny < 8 || ze - zb < 8) return cudaSuccess;
+    }
+    FastP p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm};
+    p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
+    if (vin && p.zchunk > ze - zb) p.zchunk = ze - zb;
+    cudaError_t e = cudaSuccess;
+#define CALL(KMV) \
+    e = pow2 ? dispatch_resid<KMV, true, OP_SMOOTH_NORM>(cx, p, handled) : dispatch_resid<KMV, false, OP_SMOOTH_NORM>(cx, p, handled)
     FOR_ALL_KM(CALL);
 #undef CALL
     if (e == cudaSuccess && *handled && cx.launches) ++*cx.launches;
@@ -389,6 +418,7 @@ cudaError_t kf_prepare()
             for (int nx : {64, 128}) {
                 g.nx = nx;
                 if (e == cudaSuccess) e = kf_residual(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+                if (e == cudaSuccess) e = kf_smooth_norm(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
             }
             g.nx = 0;
         }
