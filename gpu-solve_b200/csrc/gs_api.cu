@@ -365,27 +365,42 @@ int do_norm_residual(gs_handle* h)
 
 // restrict a level array onto the next level (src/cpu/CpuSolver.cpp:211-238);
 // on the first replicated level the slabs are gathered so every rank holds it whole
+// LOCAL coarse planes of level+1 this rank computes when restricting from `level`
+void coarse_range(gs_handle* h, int level, int* zb, int* ze)
+{
+    Level& F = h->lev[level];
+    Level& C = h->lev[level + 1];
+    *zb = C.ib;
+    *ze = C.ie;
+    if (partitioned(h, level) && C.replicated) {
+        // fine level in slabs, coarse level held whole: the coarse planes whose centre fine plane this rank owns
+        *zb = std::max(1, (F.zlo + 1) / 2);
+        *ze = std::min(C.g.nz + 1, (F.zhi + 1) / 2);
+    }
+}
+
+// make a freshly restricted coarse array consistent across ranks: gather the planes onto every rank on the
+// first replicated level, else refresh one ghost plane per side
+int finish_coarse(gs_handle* h, int level, double* coarse)
+{
+    Level& C = h->lev[level + 1];
+    if (partitioned(h, level) && C.replicated) {
+        if (gs_comm_gather_planes(h->comm, coarse, C.g.plane, level, h->stream) != 0)
+            return fail(GS_ECOMM, "coarse gather failed: %s", gs_comm_error(h->comm));
+        return GS_OK;
+    }
+    return exchange_halo(h, level + 1, coarse, 1);
+}
+
 int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, double* coarse2)
 {
     Level& F = h->lev[level];
     Level& C = h->lev[level + 1];
-    int zb = C.ib, ze = C.ie;
-    if (partitioned(h, level) && C.replicated) {
-        // this rank computes the coarse planes whose centre fine plane it owns
-        zb = std::max(1, (F.zlo + 1) / 2);
-        ze = std::min(C.g.nz + 1, (F.zhi + 1) / 2);
-    }
+    int zb, ze;
+    coarse_range(h, level, &zb, &ze);
     CU(ks_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2));
-    if (partitioned(h, level) && C.replicated) {
-        for (double* a : {coarse, coarse2}) {
-            if (!a) continue;
-            if (gs_comm_gather_planes(h->comm, a, C.g.plane, level, h->stream) != 0)
-                return fail(GS_ECOMM, "coarse gather failed: %s", gs_comm_error(h->comm));
-        }
-    } else {
-        GS(exchange_halo(h, level + 1, coarse, 1));
-        if (coarse2) GS(exchange_halo(h, level + 1, coarse2, 1));
-    }
+    GS(finish_coarse(h, level, coarse));
+    if (coarse2) GS(finish_coarse(h, level, coarse2));
     return GS_OK;
 }
 
@@ -393,6 +408,7 @@ int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, dou
 int do_restrict_residual(gs_handle* h, int level)
 {
     Level& L = h->lev[level];
+    Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_RESTRICT, level);
     int zb = L.ib, ze = L.ie;
     if (partitioned(h, level)) {
@@ -402,15 +418,16 @@ int do_restrict_residual(gs_handle* h, int level)
     }
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
-    if (h->opt_kernels && h->canonical && !partitioned(h, level)) {
+    if (h->opt_kernels && h->canonical) {
         // fused: the residual never goes to memory (kernels_transfer.cu)
-        Level& C = h->lev[level + 1];
+        int czb, cze;
+        coarse_range(h, level, &czb, &cze);
         bool handled = false;
-        CU(kt_resid_restrict(h->cx, km, L.pow2, L.g, C.g, C.ib, C.ie, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
-        if (handled) return GS_OK;
+        CU(kt_resid_restrict(h->cx, km, L.pow2, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
+        if (handled) return finish_coarse(h, level, C.f);
     }
     CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
-    GS(do_restrict(h, level, L.r, h->lev[level + 1].f, nullptr));
+    GS(do_restrict(h, level, L.r, C.f, nullptr));
     return GS_OK;
 }
 
@@ -421,6 +438,7 @@ int do_fas_coarse_rhs(gs_handle* h, int level)
     OpScope t(h, GS_OP_RESTRICT, level);
     GS(do_restrict(h, level, h->lev[level].v, C.restV, C.v));
     CU(ks_fas_rhs(h->cx, C.pow2, C.g, C.ib, C.ie, C.k, h->so, C.restV, C.f, C.r));
+    GS(exchange_halo(h, level + 1, C.f, 1));  // f changed on the owned planes only
     return GS_OK;
 }
 
@@ -619,6 +637,7 @@ int newton_compF(gs_handle* h, double* norm)
     {
         OpScope t(h, GS_OP_RESIDUAL, 0);
         CU(ks_newton_F(h->cx, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.newtonV, h->newtonF, L.f));
+        GS(exchange_halo(h, 0, L.f, 1));  // the residual+restriction of a slab reads f one plane outside it
     }
     GS(norm_to_host(h, 0));
     CU(cudaStreamSynchronize(h->stream));
