@@ -104,50 +104,27 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def time_cpu_reference(n, pre, post, budget_s, threads=None):
-    """the reference's CPU V-cycle (oracle/_ref when built, else the C port) on the host cores;
-    returns (vcycles_per_s at grid n, kind, cores, sample description)"""
-    orc = entry.load_oracle()
-    kind = "reference" if orc.available("reference") else "port"
-    if kind == "port" and not orc.available("port"):
-        orc.build(ref=False)
-    cores = threads or os.cpu_count()
-    sample_n = n
-    # one 511^3 V(2,2) cycle is ~9 s on 8 cores; shrink the sample (same operators, 1/8 of the points) if the budget is small
-    est = 9.0 * (n / 511.0) ** 3 * 8.0 / max(cores, 1)
-    while sample_n > 63 and est > budget_s:
-        sample_n = (sample_n + 1) // 2 - 1
+def cpu_sample_grid(n, steps_total, cores, budget_s):
+    """the largest grid, obtained by halving the target like the hierarchy does, whose CPU run fits the budget
+    (one 511^3 V(2,2) cycle is ~9 s on 8 cores)"""
+    n = tuple(n)
+    est = 9.0 * (n[0] * n[1] * n[2]) / 511.0 ** 3 * 8.0 / max(cores, 1) * steps_total
+    while min(n) > 63 and est > budget_s:
+        n = tuple((d + 1) // 2 - 1 for d in n)
         est /= 8.0
-    o = orc.Oracle(orc.make_params(sample_n, mode=0, pre=pre, post=post, maxiter=1, tol=1e-30), kind)
-    o.set_threads(cores)
-    t0 = time.time()
-    o.vcycle()
-    dt = time.time() - t0
-    o.close()
-    scale = sum(interior_points(sample_n)) / sum(interior_points(n))
-    desc = (f"1 V({pre},{post}) cycle of GpuSolve-cpu ({kind}) at n={sample_n} on {cores} threads: {dt:.2f} s"
-            + ("" if sample_n == n else f"; scaled by lattice points x{scale:.5f} to n={n}"))
-    return (1.0 / dt) * scale, kind, cores, desc
+    return n
 
 
-def run_reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return 0
-    n, pre, post = args.grid, args.pre, args.post
+def run_cpu(n, pre, post, steps, warm, budget_s):
+    """the reference's CPU V-cycle (oracle/_ref when built, else the C port) on all host threads; returns
+    (V-cycles/s on grid n, kind, cores, sample description)"""
     orc = entry.load_oracle()
     kind = "reference" if orc.available("reference") else "port"
     if kind == "port" and not orc.available("port"):
         orc.build(ref=False)
     cores = os.cpu_count()
-    steps, warm = args.steps, args.warmup
-    # bound the whole run to ~3 minutes: pick the sample grid from an 8-core estimate, refine after warm-up
-    sample_n = n
-    est = 9.0 * (n / 511.0) ** 3 * 8.0 / max(cores, 1)
-    while sample_n > 63 and est * (steps + warm) > 150.0:
-        sample_n = (sample_n + 1) // 2 - 1
-        est /= 8.0
-    o = orc.Oracle(orc.make_params(sample_n, mode=0, pre=pre, post=post, maxiter=1, tol=1e-30), kind)
+    sn = cpu_sample_grid(n, steps + warm, cores, budget_s)
+    o = orc.Oracle(orc.make_params(sn, mode=0, pre=pre, post=post, maxiter=1, tol=1e-30), kind)
     o.set_threads(cores)
     for _ in range(warm):
         o.vcycle()
@@ -156,15 +133,26 @@ def run_reference_arm(args):
         o.vcycle()
     dt = time.time() - t0
     o.close()
-    scale = sum(interior_points(sample_n)) / sum(interior_points(n))
-    value = steps / dt * scale
-    sample = (f"{steps} V({pre},{post}) cycles of GpuSolve-cpu ({kind}) at n={sample_n}, {cores} OpenMP threads"
-              + ("" if sample_n == n else f", throughput scaled by lattice points x{scale:.5f} to n={n}"))
+    scale = sum(interior_points(sn)) / sum(interior_points(tuple(n)))
+    desc = (f"{steps} V({pre},{post}) cycle(s) of GpuSolve-cpu ({kind}) at n={'x'.join(map(str, sn))} on {cores} OpenMP threads: "
+            f"{dt / steps:.2f} s per cycle" + ("" if tuple(sn) == tuple(n) else f"; throughput scaled by lattice points x{scale:.5f} "
+                                               f"to n={'x'.join(map(str, n))}"))
+    return steps / dt * scale, kind, cores, desc
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n, pre, post = resolve_grid(args), args.pre, args.post
+    steps, warm = args.steps, args.warmup
+    v, kind, cores, sample = run_cpu(n, pre, post, steps, warm, budget_s=150.0)
+    value = v * work_ratio(n)
     line = {
         "impl": "reference", "metric": "V-cycles/s at 513^3 fp64, linear V(2,2)", "value": value, "unit": "V-cycles/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3 / scale if scale else None,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic (analytic RHS)",
-        "config": workload_config(args),
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 / v,
+        "higher_is_better": True, "scaling": "weak" if args.grid is None else "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic (analytic RHS)", "config": workload_config(args),
         "cpu_baseline": {"value": value, "unit": "V-cycles/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "V-cycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -173,12 +161,48 @@ def run_reference_arm(args):
     return 0
 
 
+REF_GRID = (511, 511, 511)   # BASELINE.json configs[1]: "513^3" = 511 interior points per axis
+
+
+def default_grid(gpus):
+    """N = 1: the 513^3 grid the metric is quoted on.  N > 1: the same lattice points PER GPU (weak scaling): the grid
+    doubles along z, then y, then x, which at N = 8 is the 1025^3 grid of BASELINE.json configs[4]."""
+    g = [511, 511, 511]
+    axis, k = 2, gpus
+    while k > 1:
+        g[axis] = 2 * g[axis] + 1
+        axis = (axis - 1) % 3
+        k //= 2
+    return tuple(g)
+
+
+def resolve_grid(args):
+    if args.grid is None:
+        return default_grid(args.gpus)
+    if len(args.grid) == 1:
+        return (args.grid[0],) * 3
+    if len(args.grid) != 3:
+        raise SystemExit("--grid takes one or three integers")
+    return tuple(args.grid)
+
+
+def work_ratio(n):
+    """lattice points of all levels relative to the 513^3 reference grid: 1 for the headline grid"""
+    return sum(interior_points(n)) / sum(interior_points(REF_GRID))
+
+
 def workload_config(args):
-    n = args.grid
-    return {"workload": f"linear Poisson 7-point, n={n} interior ({n + 2}^3 arrays), V({args.pre},{args.post}) cycles, fp64, omega 0.8",
-            "grid": [n, n, n], "mode": 0, "pre": args.pre, "post": args.post,
-            "l2": "inputs larger than L2 (each level-0 array is %.2f GB)" % ((n + 2) ** 3 * 8 / 1e9),
-            "partition": "single GPU" if args.gpus == 1 else f"z-slabs over {args.gpus} GPUs, NCCL halo exchange, coarse levels replicated"}
+    n = resolve_grid(args)
+    arr = "x".join(str(d + 2) for d in n)
+    cfg = {"workload": f"linear Poisson 7-point, n={'x'.join(map(str, n))} interior ({arr} arrays), V({args.pre},{args.post}) cycles, "
+                       f"fp64, omega 0.8",
+           "grid": list(n), "mode": 0, "pre": args.pre, "post": args.post,
+           "l2": "inputs larger than L2 (each level-0 array is %.2f GB)" % ((n[0] + 2) * (n[1] + 2) * (n[2] + 2) * 8 / 1e9),
+           "partition": "single GPU" if args.gpus == 1 else f"z-slabs over {args.gpus} GPUs, NCCL halo exchange, coarse levels replicated"}
+    if n != REF_GRID:
+        cfg["value_normalisation"] = ("value = V-cycles/s on this grid x %.4f (its lattice points over all levels / those of the 513^3 "
+                                      "grid): whole-job throughput in 513^3-equivalent V-cycles/s" % work_ratio(n))
+    return cfg
 
 
 def main():
@@ -187,7 +211,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--grid", type=int, default=511, help="interior points per axis (511 -> 513^3 arrays; 1023 -> 1025^3)")
+    ap.add_argument("--grid", type=int, nargs="+", default=None,
+                    help="interior points per axis, one or three integers (511 -> 513^3 arrays; 1023 -> 1025^3); default: 511^3 per GPU")
     ap.add_argument("--pre", type=int, default=2)
     ap.add_argument("--post", type=int, default=2)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -218,7 +243,8 @@ def main():
         dist.broadcast_object_list(box, src=0)
         nccl_id = box[0]
 
-    n, pre, post = args.grid, args.pre, args.post
+    n, pre, post = resolve_grid(args), args.pre, args.post
+    wr = work_ratio(n)
     p = gs.make_params(n, mode=0, pre=pre, post=post, maxiter=1, tol=1e-30)
     solver = gs.GpuSolve(p, device=local_rank, rank=rank, world=world, nccl_id=nccl_id)
     stream = torch.cuda.ExternalStream(solver.stream, device=torch.device("cuda", local_rank))
@@ -252,7 +278,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     ms_per_step = ms / args.steps
-    value = 1e3 / ms_per_step
+    value = 1e3 / ms_per_step * wr
 
     # ---- dominant kernel (fine-level smoother sweep) inside the V-cycle, per-operator CUDA events ----
     solver.set_option("timing", 1)
@@ -273,7 +299,7 @@ def main():
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as f:
-            traffic = json.load(f).get(f"smooth_n{n}", None)
+            traffic = json.load(f).get("smooth_n%d" % n[0], None) if n == REF_GRID else None
     roofline = {"bound": "hbm", "kernel": "fine-level damped-Jacobi sweep (level 0, inside the V-cycle)", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": sweep_bytes, "ms_per_launch": sweep_ms,
@@ -304,26 +330,27 @@ def main():
             t = torch.tensor([dt], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e2e = {"value": k / dt, "unit": "V-cycles/s", "h2d_bytes_per_step": int(np.prod(shape)) * 8 // 1, "d2h_bytes_per_step": 8,
+        e2e = {"value": k / dt * wr, "unit": "V-cycles/s", "h2d_bytes_per_step": int(np.prod(shape)) * 8 // 1, "d2h_bytes_per_step": 8,
                "steps": k, "note": "gs_set_field(F) from pinned host memory + gs_vcycle + norm read-back per step"}
         del f_host
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, kind, cores, sample = time_cpu_reference(n, pre, post, budget_s=30.0)
-        cpu = {"value": v, "unit": "V-cycles/s", "cores": cores, "kind": kind, "sample": sample}
+        v, kind, cores, sample = run_cpu(n, pre, post, 1, 0, budget_s=30.0)
+        cpu = {"value": v * wr, "unit": "V-cycles/s", "cores": cores, "kind": kind, "sample": sample}
 
     if rank == 0:
         line = {
-            "metric": "V-cycles/s at 513^3 fp64, linear V(2,2)" if n == 511 else f"V-cycles/s at {n + 2}^3 fp64, linear V({pre},{post})",
+            "metric": "V-cycles/s at 513^3 fp64, linear V(2,2)" if (pre, post) == (2, 2) else f"V-cycles/s at 513^3 fp64, linear V({pre},{post})",
             "value": value, "unit": "V-cycles/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if args.grid is None else "strong",
+            "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (analytic RHS, src/cpu/CpuGridData.cpp:47-58)", "config": workload_config(args),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "vcycle": {"algorithmic_bytes": vbytes, "achieved_gbs": vbytes / (ms_per_step * 1e-3) / 1e9,
                        "frac_of_peak": vbytes / (ms_per_step * 1e-3) / 1e9 / peak, "per_operator": per_op,
                        "glups_smoother_equivalent": (pre + post) * sum(P) / (ms_per_step * 1e-3) / 1e9},
-            "final_residual_norm": norm,
+            "final_residual_norm": norm, "vcycles_per_s_on_this_grid": 1e3 / ms_per_step, "work_ratio_vs_513": wr,
         }
         print(json.dumps(line), flush=True)
     solver.close()

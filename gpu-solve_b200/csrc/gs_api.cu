@@ -94,6 +94,8 @@ struct gs_handle {
     std::vector<uint64_t> lvl_launches;  // [level][op]
     GsComm* comm;
     int replicated_from;
+    double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
+    size_t stage_count;
 };
 
 namespace {
@@ -731,6 +733,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_fuse_norm = 1;
     h->comm = nullptr;
     h->h_norm = nullptr;
+    h->stage = nullptr;
+    h->stage_count = 0;
     memset(h->op_ms, 0, sizeof h->op_ms);
     memset(h->op_launches, 0, sizeof h->op_launches);
     for (int i = 0; i < 7; i++) {
@@ -929,6 +933,7 @@ int gs_destroy(gs_handle* h)
         for (double* a : {L.v, L.vtmp, L.f, L.r, L.restV, L.newtonV, L.coef})
             if (a) cudaFree(a);
     if (h->newtonF) cudaFree(h->newtonF);
+    if (h->stage) cudaFree(h->stage);
     if (h->cx.norm.partials) cudaFree(h->cx.norm.partials);
     if (h->cx.norm.ticket) cudaFree(h->cx.norm.ticket);
     if (h->cx.norm.result) cudaFree(h->cx.norm.result);
@@ -976,6 +981,39 @@ int gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hv
     return GS_OK;
 }
 
+// dense host planes <-> padded device planes through a flat device staging buffer: the PCIe transfer is one
+// contiguous copy per chunk (full link speed), the pitch conversion is a device-to-device 2-D copy in HBM
+static int staged_copy(gs_handle* h, const Geom& g, double* dev, double* dense, size_t nplanes, bool to_host)
+{
+    const size_t XY = (size_t)g.X * g.Y;
+    size_t want = std::max<size_t>(XY, (size_t)8 << 20);  // 64 MB of doubles, or one plane if that is larger
+    want = std::min(want, XY * nplanes);
+    if (h->stage_count < want) {
+        if (h->stage) cudaFree(h->stage);
+        h->stage = nullptr;
+        h->stage_count = 0;
+        if (cudaMalloc((void**)&h->stage, want * sizeof(double)) != cudaSuccess)
+            return fail(GS_ENOMEM, "staging buffer of %zu bytes", want * sizeof(double));
+        h->stage_count = want;
+    }
+    const size_t ppc = std::max<size_t>(1, h->stage_count / XY);
+    for (size_t p0 = 0; p0 < nplanes; p0 += ppc) {
+        const size_t n = std::min(ppc, nplanes - p0);
+        double* d = dev + GS_XOFF + p0 * (size_t)g.plane;
+        double* hp = dense + p0 * XY;
+        if (to_host) {
+            CU(cudaMemcpy2DAsync(h->stage, g.X * sizeof(double), d, g.pitch * sizeof(double), g.X * sizeof(double), g.Y * n,
+                                 cudaMemcpyDeviceToDevice, h->stream));
+            CU(cudaMemcpyAsync(hp, h->stage, n * XY * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        } else {
+            CU(cudaMemcpyAsync(h->stage, hp, n * XY * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            CU(cudaMemcpy2DAsync(d, g.pitch * sizeof(double), h->stage, g.X * sizeof(double), g.X * sizeof(double), g.Y * n,
+                                 cudaMemcpyDeviceToDevice, h->stream));
+        }
+    }
+    return GS_OK;
+}
+
 // dense host array <-> padded device slab; z-fastest is transposed on the host
 static int field_io(gs_handle* h, int level, int field, double* host, int layout, bool to_host)
 {
@@ -1006,8 +1044,7 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
             int rc = gs_comm_gather_to_host(h->comm, *slot, g.plane, g.pitch, g.z0, level, dense, X, Y, Z, h->stream);
             if (rc != 0) return fail(GS_ECOMM, "field gather failed: %s", gs_comm_error(h->comm));
         } else {
-            CU(cudaMemcpy2DAsync(dense, X * sizeof(double), *slot + GS_XOFF, g.pitch * sizeof(double), X * sizeof(double), Y * Z,
-                                 cudaMemcpyDeviceToHost, h->stream));
+            GS(staged_copy(h, g, *slot, dense, Z, true));
             CU(cudaStreamSynchronize(h->stream));
         }
         if (layout == GS_LAYOUT_Z_FASTEST)
@@ -1016,14 +1053,11 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
                     for (size_t z = 0; z < Z; z++) host[z + Z * (y + Y * x)] = dense[x + X * (y + Y * z)];
     } else {
         // local planes [z0, z0+nzl) of the dense array (ghost planes included, so they start consistent)
-        const double* src = dense + X * Y * (size_t)g.z0;
-        std::vector<double*> dst = {*slot};
-        if (field == GS_FIELD_V) dst.push_back(L.vtmp);  // keep the halo of both ping-pong buffers identical
-        // on the handle's own (non-blocking) stream: a legacy-stream cudaMemcpy2D from pageable memory returns
-        // once the data is staged, and the DMA would race with the next kernel queued on h->stream
-        for (double* d : dst)
-            CU(cudaMemcpy2DAsync(d + GS_XOFF, g.pitch * sizeof(double), src, X * sizeof(double), X * sizeof(double),
-                                 Y * (size_t)g.nzl, cudaMemcpyHostToDevice, h->stream));
+        // everything on the handle's own (non-blocking) stream: a legacy-stream cudaMemcpy from pageable memory
+        // returns once the data is staged, and the DMA would race with the next kernel queued on h->stream
+        GS(staged_copy(h, g, *slot, dense + X * Y * (size_t)g.z0, (size_t)g.nzl, false));
+        if (field == GS_FIELD_V)  // keep the halo of both ping-pong buffers identical
+            CU(cudaMemcpyAsync(L.vtmp, L.v, L.count * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
         CU(cudaStreamSynchronize(h->stream));
         L.pre_valid = false;
         if (field == GS_FIELD_NEWTONV) L.coef_valid = false;
