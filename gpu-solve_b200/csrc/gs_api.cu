@@ -61,7 +61,7 @@ struct Level {
     size_t count;     // doubles per array
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
     bool coef_valid;
-    bool pre_valid;   // vtmp == one Jacobi sweep of v for the current f/aux (written by the fused sweep+norm kernel)
+    int pre_valid;    // vtmp == this many Jacobi sweeps of v for the current f/aux (written by the fused sweep+norm kernels)
 };
 
 struct EventPair {
@@ -84,7 +84,8 @@ struct gs_handle {
     int opt_kernels, opt_graph, opt_timing, opt_fuse_norm;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
-    std::map<uint64_t, bool> graphs_pre_valid;     // lev[0].pre_valid after a replay of each graph
+    std::map<uint64_t, int> graphs_pre_valid;      // lev[0].pre_valid after a replay of each graph
+    std::map<uint64_t, uint64_t> graphs_swapped;   // bit l: level l ends a replay with v and vtmp exchanged
     std::vector<double> history;
     std::vector<EventPair> ev_used;
     std::vector<cudaEvent_t> ev_free;
@@ -300,19 +301,28 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     const int km = smoother_km(h);
     if (km == KM_NEWTON_COEF && iters > 0) GS(ensure_coef(h, level));
     OpScope t(h, GS_OP_SMOOTH, level);
-    if (L.pre_valid && iters > 0) {
-        // the first sweep was already produced together with the last residual norm (do_norm_residual)
-        L.pre_valid = false;
+    if (L.pre_valid > 0 && iters >= (uint64_t)L.pre_valid) {
+        // the first sweep(s) were already produced together with the last residual norm (do_norm_residual)
+        iters -= L.pre_valid;
+        L.pre_valid = 0;
         std::swap(L.v, L.vtmp);
         GS(exchange_halo(h, level, L.v, 1));
-        iters--;
     }
-    for (uint64_t it = 0; it < iters; it++) {
+    L.pre_valid = 0;
+    const double* aux = smoother_aux(h, level, km);
+    while (iters > 0) {
         bool handled = false;
-        if (h->opt_kernels && h->canonical)
-            CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, smoother_aux(h, level, km), &handled));
-        if (!handled)
-            CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, smoother_aux(h, level, km)));
+        if (iters >= 2 && h->opt_kernels && h->canonical) {
+            // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
+            if (partitioned(h, level) && h->cx.tune.fuse2) GS(exchange_halo(h, level, L.v, 2));
+            CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
+            if (handled) iters -= 2;
+        }
+        if (!handled) {
+            if (h->opt_kernels && h->canonical) CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
+            if (!handled) CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, aux));
+            iters--;
+        }
         std::swap(L.v, L.vtmp);
         GS(exchange_halo(h, level, L.v, 1));
     }
@@ -356,9 +366,18 @@ int do_norm_residual(gs_handle* h)
         if (km == KM_NEWTON_COEF) GS(ensure_coef(h, 0));
         OpScope t(h, GS_OP_RESIDUAL, 0);
         bool handled = false;
-        CU(kf_smooth_norm(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, smoother_aux(h, 0, km), &handled));
+        const double* aux = smoother_aux(h, 0, km);
+        if (h->p.pre >= 2) {
+            if (partitioned(h, 0) && h->cx.tune.fuse2) GS(exchange_halo(h, 0, L.v, 2));
+            CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, &handled));
+            if (handled) {
+                L.pre_valid = 2;
+                return GS_OK;
+            }
+        }
+        CU(kf_smooth_norm(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
         if (handled) {
-            L.pre_valid = true;
+            L.pre_valid = 1;
             return GS_OK;
         }
     }
@@ -450,7 +469,7 @@ int do_prolong_correct(gs_handle* h, int level)
     Level& F = h->lev[level];
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_PROLONG, level);
-    F.pre_valid = false;
+    F.pre_valid = 0;
     if (h->p.mode == GS_MODE_NONLINEAR) {
         CU(ks_axpy(h->cx, C.g, 0, C.g.nzl, C.v, C.restV, -1));
     }
@@ -508,7 +527,8 @@ uint64_t parity_key(const gs_handle* h)
     key |= (uint64_t)(h->cx.tune.smooth_variant & 0x3f) << 32;
     key ^= (uint64_t)(h->cx.tune.zchunk & 0xfff) << 20;
     key ^= (uint64_t)(h->cx.tune.rr_variant & 1) << 19;
-    key ^= (uint64_t)(h->lev[0].pre_valid ? 1 : 0) << 18;
+    key ^= (uint64_t)(h->lev[0].pre_valid & 3) << 15;
+    key ^= (uint64_t)(h->cx.tune.fuse2 & 7) << 12;
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
@@ -533,19 +553,21 @@ int run_vcycle(gs_handle* h, double* norm)
                 t0.push_back(L.vtmp);
             }
             const uint64_t l0 = h->launches;
-            const bool pre0 = h->lev[0].pre_valid;
+            const int pre0 = h->lev[0].pre_valid;
             cudaGraph_t g = nullptr;
             CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             int rc = enqueue_vcycle(h);
             cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
             // capture ran the host-side pointer swaps once; undo them, the launch below redoes them
+            uint64_t swapped = 0;
             for (size_t l = 0; l < h->lev.size(); l++) {
+                if (h->lev[l].v != v0[l]) swapped |= 1ull << l;
                 h->lev[l].v = v0[l];
                 h->lev[l].vtmp = t0[l];
             }
             uint64_t per_cycle = h->launches - l0;
             h->launches = l0;
-            const bool pre1 = h->lev[0].pre_valid;
+            const int pre1 = h->lev[0].pre_valid;
             h->lev[0].pre_valid = pre0;
             if (rc != GS_OK) {
                 if (g) cudaGraphDestroy(g);
@@ -558,15 +580,15 @@ int run_vcycle(gs_handle* h, double* norm)
             it = h->graphs.emplace(key, ex).first;
             h->graphs_launches[key] = per_cycle;
             h->graphs_pre_valid[key] = pre1;
+            h->graphs_swapped[key] = swapped;
         }
         CU(cudaGraphLaunch(it->second, h->stream));
         h->launches += h->graphs_launches[key];
         h->lev[0].pre_valid = h->graphs_pre_valid[key];
-        // host-side view of the buffer parity after the cycle
-        const int last = (int)h->lev.size() - 1;
-        const bool odd = ((h->p.pre + h->p.post) & 1) != 0;
-        (void)last;
-        (void)odd;  // parity is restored by construction (do_prolong_correct / coarsest copy)
+        // host-side view of the buffer parity after the cycle (the graph is keyed by the parity it starts from)
+        const uint64_t swapped = h->graphs_swapped[key];
+        for (size_t l = 0; l < h->lev.size(); l++)
+            if (swapped >> l & 1) std::swap(h->lev[l].v, h->lev[l].vtmp);
     }
     CU(cudaStreamSynchronize(h->stream));
     *norm = sqrt(*h->h_norm);
@@ -833,9 +855,14 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* ev = getenv("GPUSOLVE_ZCHUNK")) h->cx.tune.zchunk = std::max(1, atoi(ev));
     if (const char* ev = getenv("GPUSOLVE_FAST_MIN_N")) h->cx.tune.fast_min_n = atoi(ev);
     h->cx.tune.rr_variant = 0;
+    h->cx.tune.fuse2 = 1;
+    h->cx.tune.fuse2_min_n = 96;
+    h->cx.tune.zchunk2 = 128;
+    if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(3, atoi(ev)));
     if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = atoi(ev) != 0;
     e = kf_prepare();
     if (e == cudaSuccess) e = kt_prepare();
+    if (e == cudaSuccess) e = kx_prepare();
     if (e != cudaSuccess) {
         gs_destroy(h);
         return fail(GS_ECUDA, "kernel setup failed: %s", cudaGetErrorString(e));
@@ -1308,6 +1335,11 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
     else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
+    else if (n == "fuse2") {
+        h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(3, value));
+        h->lev[0].pre_valid = 0;
+    } else if (n == "fuse2_min_n") h->cx.tune.fuse2_min_n = (int)value;
+    else if (n == "zchunk2") h->cx.tune.zchunk2 = (int)std::max<int64_t>(8, value);
     else return fail(GS_EINVAL, "unknown option \"%s\"", name);
     return GS_OK;
 }

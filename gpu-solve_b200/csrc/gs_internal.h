@@ -64,6 +64,9 @@ struct Tune {
     int zchunk;          // planes per CTA of the z-marching kernels
     int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
     int rr_variant;      // tile of the fused residual+restriction kernel: 0 = 32x8 coarse columns, 1 = 32x4
+    int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1.. = tile variant + 1
+    int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
+    int zchunk2;         // planes per CTA of the two-sweep kernel
 };
 
 struct LaunchCtx {
@@ -113,6 +116,13 @@ cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
 // vout = sweep(vin) and sum of squares of the residual of vin -> cx.norm.result
 cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
                            const double* vin, double* vout, const double* f, const double* aux, bool* handled);
+
+// ---- kernels_fused.cu: two Jacobi sweeps per pass (temporal blocking, bit-identical to two single sweeps) ----
+cudaError_t kx_prepare();
+// vout = S(S(vin)) on local planes [zb, ze); needs two valid planes of vin outside the range.  with_norm: also
+// sum of squares of the residual of vin -> cx.norm.result
+cudaError_t kx_smooth2(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                       const double* vin, double* vout, const double* f, const double* aux, bool with_norm, bool* handled);
 
 // ---- kernels_transfer.cu: tuned grid-transfer kernels (canonical stencil) ----
 cudaError_t kt_prepare();

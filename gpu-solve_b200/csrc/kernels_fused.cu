@@ -1,0 +1,286 @@
+// kernels_fused.cu — temporally blocked smoother for sm_100a (canonical 7-point stencil):
+// TWO damped-Jacobi sweeps per pass over the level.
+//
+//   smooth2_tma   v'' = S(S(v))   (src/cpu/CpuSolver.cpp:141-179 applied twice)
+//                 24 B per lattice point for two sweeps (read v, read f, write v''), i.e.
+//                 12 B per lattice update instead of 24.
+//
+// Jacobi is order-independent (the reference computes r of the whole level before it touches
+// v, src/cpu/CpuSolver.cpp:149-177), so the second sweep of a point may run as soon as the
+// first sweep of its seven neighbours is known.  A CTA owns a 60 x TY output tile, marches
+// along z and keeps a two-deep wavefront:
+//   * one producer warp streams the v tile with a two-cell rim (64 x (TY+4) box) and the f tile
+//     with a one-cell rim (64 x (TY+2) box) of every plane into a shared-memory ring with TMA
+//     (cp.async.bulk.tensor.3d, full/empty mbarriers);
+//   * a consumer thread owns two y-adjacent columns of the 62 x (TY+2) first-sweep region with
+//     register queues along z for the input and for the first-sweep values of its own columns;
+//     first-sweep planes go through a two-slot shared-memory ring so that the in-plane
+//     neighbours of the second sweep can be read one plane later (one named barrier per plane);
+//   * first-sweep values outside the interior are forced to zero — what the unfused path reads
+//     from the halo of the ping-pong buffer.
+// Per-point arithmetic is point_update of kernels_fast.cu (canon_residual + jacobi_update,
+// -fmad=false): every intermediate and final value is bit-identical to two single sweeps.
+// With NORM the kernel also returns sum r^2 of the INPUT iterate (the first sweep's residual),
+// each point counted by the CTA whose output tile holds it.
+#include <cuda.h>
+
+#include "gs_device.cuh"
+
+namespace {
+
+struct Fused2P {
+    Geom g;
+    PointK k;
+    int zb, ze, zchunk;  // LOCAL planes [zb, ze) to update, planes per CTA
+    const double* vin;
+    double* vout;
+    const double* f;
+    const double* aux;
+    NormBuf nb;
+};
+
+template <int TY, int NSTAGE>
+struct S2Cfg {
+    static constexpr int BW = 64;    // box width: columns x0-2 .. x0+61
+    static constexpr int TXO = 60;   // output columns x0 .. x0+59
+    static constexpr int VH = TY + 4, FH = TY + 2;
+    static constexpr int V_BYTES = BW * VH * 8, F_BYTES = BW * FH * 8;  // multiples of 512
+    static constexpr int STAGE = V_BYTES + F_BYTES;
+    static constexpr int S1_BYTES = BW * FH * 8;
+    static constexpr int NCONS = BW * FH / 2;  // two first-sweep rows per thread
+    static constexpr int THREADS = NCONS + 32;
+    static constexpr int SMEM = NSTAGE * STAGE + 2 * S1_BYTES + 2 * NSTAGE * 8 + 128;
+    static_assert(TY % 2 == 0, "two rows per thread");
+    static_assert(NCONS % 32 == 0 && NCONS <= 992, "consumer threads");
+};
+
+template <int KM, bool POW2, bool NORM, int TY, int NSTAGE>
+__global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(const __grid_constant__ CUtensorMap map_v,
+                                                                           const __grid_constant__ CUtensorMap map_f, Fused2P p)
+{
+    using Cfg = S2Cfg<TY, NSTAGE>;
+    constexpr int BW = Cfg::BW;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+    double* s1ring = (double*)(smem + NSTAGE * Cfg::STAGE);
+    uint64_t* full = (uint64_t*)(smem + NSTAGE * Cfg::STAGE + 2 * Cfg::S1_BYTES);
+    uint64_t* empty = full + NSTAGE;
+
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * Cfg::TXO + 1, y0 = blockIdx.y * TY + 1;  // first output point of the tile
+    const int z0 = p.zb + blockIdx.z * p.zchunk;
+    const int z1 = min(z0 + p.zchunk, p.ze);
+    const int nzo = z1 - z0;      // planes this CTA writes
+    // plane index q: local plane z0-2+q.  v planes q = 0 .. nzo+3, f planes q = 1 .. nzo+2,
+    // first sweep on q = 1 .. nzo+2, second sweep on q = 2 .. nzo+1
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], Cfg::NCONS / 32);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (tid >= Cfg::NCONS) {
+        if (tid == Cfg::NCONS) {
+            for (int q = 0; q < nzo + 4; q++) {
+                const int s = q % NSTAGE;
+                if (q >= NSTAGE) mbar_wait(&empty[s], ((q / NSTAGE) - 1) & 1);
+                const bool has_f = q >= 1 && q <= nzo + 2;
+                mbar_expect_tx(&full[s], Cfg::V_BYTES + (has_f ? Cfg::F_BYTES : 0));
+                unsigned char* st = smem + s * Cfg::STAGE;
+                // out-of-range rows / planes / columns (negative or past the array) are zero-filled by TMA
+                tma_load_3d(st, &map_v, &full[s], GS_XOFF + x0 - 2, y0 - 2, z0 - 2 + q);
+                if (has_f) tma_load_3d(st + Cfg::V_BYTES, &map_f, &full[s], GS_XOFF + x0 - 2, y0 - 1, z0 - 2 + q);
+            }
+        }
+        return;
+    }
+
+    // ---- consumers ----
+    const int lx = tid & (BW - 1), tr = tid / BW;
+    constexpr int LAST_TR = Cfg::FH / 2 - 1;
+    const int x = x0 - 2 + lx;
+    const int ya = y0 - 1 + 2 * tr, yb = ya + 1;
+    const int iv = (2 * tr + 1) * BW + lx;  // (x, ya) inside a v box; (x, yb) = iv + BW
+    const int is = (2 * tr) * BW + lx;      // (x, ya) inside an f box / first-sweep slot
+    // first sweep defined (else the value is the zero of the Dirichlet halo)
+    const bool x1ok = lx >= 1 && lx <= BW - 2 && x >= 1 && x <= p.g.nx;
+    const bool a1 = x1ok && ya >= 1 && ya <= p.g.ny;
+    const bool b1 = x1ok && yb <= p.g.ny;
+    // points of the output tile
+    const bool xo = lx >= 2 && lx <= BW - 3 && x <= p.g.nx;
+    const bool oa = xo && tr > 0 && ya <= p.g.ny;
+    const bool ob = xo && tr < LAST_TR && yb <= p.g.ny;
+    const int isS = tr > 0 ? is - BW : is;                  // south of row a (unused when tr == 0)
+    const int isN = tr < LAST_TR ? is + 2 * BW : is + BW;   // north of row b (unused when tr == LAST_TR)
+    const int eo = lx < BW - 1 ? 1 : 0, wo = lx > 0 ? 1 : 0;  // the box-edge lanes own no first-sweep point: keep their reads inside
+    const int lane0 = (tid & 31) == 0;
+    const i64 plane = p.g.plane;
+    i64 ca = gs_idx(p.g, min(max(x, 1), p.g.nx), min(max(ya, 1), p.g.ny), z0 - 2);  // plane q = 0
+    const i64 ab = (yb <= p.g.ny && ya >= 1) ? p.g.pitch : 0;                    // offset of row b from row a
+    const int zg0 = p.g.z0 + z0 - 2;  // global plane of q = 0
+
+    auto vbox = [&](int q) { return (const double*)(smem + (q % NSTAGE) * Cfg::STAGE); };
+    auto fbox = [&](int q) { return (const double*)(smem + (q % NSTAGE) * Cfg::STAGE + Cfg::V_BYTES); };
+    auto s1slot = [&](int q) { return s1ring + (q & 1) * (Cfg::S1_BYTES / 8); };
+
+    double sq = 0.0;
+    mbar_wait(&full[0], 0);
+    double Da = vbox(0)[iv], Db = vbox(0)[iv + BW];
+    __syncwarp();
+    if (lane0) mbar_arrive(&empty[0]);
+    mbar_wait(&full[1 % NSTAGE], (1 / NSTAGE) & 1);
+    double Ca = vbox(1)[iv], Cb = vbox(1)[iv + BW];
+    double D1a = 0.0, D1b = 0.0, C1a = 0.0, C1b = 0.0;  // first-sweep values of the own columns
+    double fpa = 0.0, fpb = 0.0, xpa = 0.0, xpb = 0.0;  // f / aux of the previous plane
+
+    for (int q = 1; q <= nzo + 2; q++) {
+        ca += plane;  // (x, ya) on plane q
+        double xa = 0.0, xb = 0.0;
+        const int zg = zg0 + q;
+        const bool zok = zg >= 1 && zg <= p.g.nz;
+        if (KM >= KM_NEWTON_EXP) {
+            if (a1 && zok) xa = p.aux[ca];
+            if (b1 && zok) xb = p.aux[ca + ab];
+        }
+        mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
+        const double* vb = vbox(q);
+        const double* vu = vbox(q + 1);
+        const double Ua = vu[iv], Ub = vu[iv + BW];
+        const double Ea = vb[iv + eo], Wa = vb[iv - wo], Sa = vb[iv - BW];
+        const double Eb = vb[iv + BW + eo], Wb = vb[iv + BW - wo], Nb = vb[iv + 2 * BW];
+        const double fa = fbox(q)[is], fb = fbox(q)[is + BW];
+        __syncwarp();
+        if (lane0) mbar_arrive(&empty[q % NSTAGE]);
+
+        // ---- first sweep on plane q ----
+        double dena, denb;
+        const double ra = canon_residual<KM, POW2>(Ca, Ea, Wa, Cb, Sa, Ua, Da, fa, xa, p.k, dena);
+        const double rb = canon_residual<KM, POW2>(Cb, Eb, Wb, Nb, Ca, Ub, Db, fb, xb, p.k, denb);
+        double U1a = jacobi_update<KM>(Ca, ra, dena, p.k);
+        double U1b = jacobi_update<KM>(Cb, rb, denb, p.k);
+        U1a = (a1 && zok) ? U1a : 0.0;
+        U1b = (b1 && zok) ? U1b : 0.0;
+        if (NORM && q >= 2 && q <= nzo + 1) {
+            if (oa) sq += ra * ra;
+            if (ob) sq += rb * rb;
+        }
+        double* sw = s1slot(q);
+        sw[is] = U1a;
+        sw[is + BW] = U1b;
+
+        // ---- second sweep on plane q-1 (its first-sweep neighbours were stored one iteration ago) ----
+        if (q >= 3) {
+            const double* sr = s1slot(q - 1);
+            const double E1a = sr[is + eo], W1a = sr[is - wo], S1a = sr[isS];
+            const double E1b = sr[is + BW + eo], W1b = sr[is + BW - wo], N1b = sr[isN];
+            double d2;
+            const double r2a = canon_residual<KM, POW2>(C1a, E1a, W1a, C1b, S1a, U1a, D1a, fpa, xpa, p.k, d2);
+            const double na = jacobi_update<KM>(C1a, r2a, d2, p.k);
+            const double r2b = canon_residual<KM, POW2>(C1b, E1b, W1b, N1b, C1a, U1b, D1b, fpb, xpb, p.k, d2);
+            const double nb = jacobi_update<KM>(C1b, r2b, d2, p.k);
+            if (oa) p.vout[ca - plane] = na;
+            if (ob) p.vout[ca - plane + ab] = nb;
+        }
+        Da = Ca; Ca = Ua; Db = Cb; Cb = Ub;
+        D1a = C1a; C1a = U1a; D1b = C1b; C1b = U1b;
+        fpa = fa; fpb = fb; xpa = xa; xpb = xb;
+        consumer_sync<Cfg::NCONS>();
+    }
+    if (NORM) {
+        __shared__ double sh[32];
+        const double tot = block_sum<Cfg::NCONS>(sq, sh, tid);
+        grid_sum_finish<Cfg::NCONS>(tot, p.nb, sh, tid);
+    }
+}
+
+template <int KM, bool POW2, bool NORM, int TY, int NSTAGE>
+cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
+{
+    using Cfg = S2Cfg<TY, NSTAGE>;
+    static bool prepared = false;
+    if (!prepared) {
+        cudaError_t e = cudaFuncSetAttribute(smooth2_tma<KM, POW2, NORM, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::SMEM);
+        if (e != cudaSuccess) return e;
+        prepared = true;
+    }
+    if (!p.vin) return cudaSuccess;  // preparation call
+    CUtensorMap mv, mf;
+    if (!gs_tensor_map(p.vin, p.g, Cfg::BW, Cfg::VH, &mv) || !gs_tensor_map(p.f, p.g, Cfg::BW, Cfg::FH, &mf)) return cudaSuccess;
+    const int tx = (p.g.nx + Cfg::TXO - 1) / Cfg::TXO, ty = (p.g.ny + TY - 1) / TY;
+    // every chunk re-reads four planes and recomputes two first-sweep planes: keep chunks long
+    const int planes = p.ze - p.zb;
+    const int want = (cx.sm_count * 4 + tx * ty - 1) / (tx * ty);
+    int chunk = (planes + want - 1) / want;
+    chunk = max(chunk, min(planes, 32));
+    chunk = min(chunk, p.zchunk);
+    p.zchunk = chunk;
+    dim3 grid(tx, ty, (planes + chunk - 1) / chunk);
+    if (NORM && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;
+    smooth2_tma<KM, POW2, NORM, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    *handled = true;
+    return cudaGetLastError();
+}
+
+template <int KM, bool POW2, bool NORM>
+cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool* handled)
+{
+    switch (variant) {
+    case 1: return launch_s2<KM, POW2, NORM, 14, 3>(cx, p, handled);
+    case 2: return launch_s2<KM, POW2, NORM, 22, 3>(cx, p, handled);
+    default: return launch_s2<KM, POW2, NORM, 14, 4>(cx, p, handled);
+    }
+}
+
+}  // namespace
+
+// vout = S(S(vin)); with_norm: also sum r(vin)^2 -> cx.norm.result.  The level must hold two valid
+// planes of vin and one of f (and aux) outside [zb, ze).
+cudaError_t kx_smooth2(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
+                       double* vout, const double* f, const double* aux, bool with_norm, bool* handled)
+{
+    *handled = false;
+    if (vin) {
+        if (ze <= zb || cx.tune.fuse2 == 0) return cudaSuccess;
+        if (g.nx < cx.tune.fuse2_min_n || g.ny < 16 || ze - zb < 16) return cudaSuccess;  // small levels: single sweeps
+    }
+    Fused2P p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm};
+    p.zchunk = cx.tune.zchunk2 > 0 ? cx.tune.zchunk2 : 128;
+    const int lo = vin ? cx.tune.fuse2 - 1 : 0, hi = vin ? cx.tune.fuse2 - 1 : 2;
+    cudaError_t e = cudaSuccess;
+    for (int var = lo; var <= hi && e == cudaSuccess; var++) {
+#define CALL(KMV)                                                                                          \
+    e = with_norm ? (pow2 ? dispatch_s2<KMV, true, true>(cx, p, var, handled) : dispatch_s2<KMV, false, true>(cx, p, var, handled)) \
+                  : (pow2 ? dispatch_s2<KMV, true, false>(cx, p, var, handled) : dispatch_s2<KMV, false, false>(cx, p, var, handled))
+        switch (km) {
+        case KM_LINEAR: CALL(KM_LINEAR); break;
+        case KM_NONLINEAR: CALL(KM_NONLINEAR); break;
+        case KM_NEWTON_EXP: CALL(KM_NEWTON_EXP); break;
+        default: CALL(KM_NEWTON_COEF); break;
+        }
+#undef CALL
+    }
+    if (e == cudaSuccess && *handled && cx.launches) ++*cx.launches;
+    return e;
+}
+
+cudaError_t kx_prepare()
+{
+    static bool done = false;
+    if (done) return cudaSuccess;
+    LaunchCtx cx{};
+    Geom g{};
+    PointK k{};
+    bool handled;
+    cudaError_t e = cudaSuccess;
+    for (int km = 0; km < 4 && e == cudaSuccess; km++)
+        for (int pw = 0; pw < 2 && e == cudaSuccess; pw++)
+            for (int nm = 0; nm < 2 && e == cudaSuccess; nm++)
+                e = kx_smooth2(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, &handled);
+    done = e == cudaSuccess;
+    return e;
+}

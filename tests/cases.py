@@ -47,6 +47,11 @@ BIG_CASES = {
     "lin127_v33": dict(n=127, mode=0, pre=3, post=3, maxiter=2, tol=1e-30),
     "nl127_v22": dict(n=127, mode=1, pre=2, post=2, maxiter=1, tol=1e-30),
     "shipped127": dict(n=127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5),  # examples/data-2nd_order.conf
+    # two-sweeps-per-pass smoother (kernels_fused.cu) on the finest levels: even sweep counts, partial tiles
+    "lin127_v22": dict(n=127, mode=0, pre=2, post=2, maxiter=3, tol=1e-30),
+    "lin_wide_v44": dict(n=(131, 97, 63), mode=0, pre=4, post=4, maxiter=2, tol=1e-30),
+    "nl_wide_v42": dict(n=(121, 64, 70), mode=1, pre=4, post=2, maxiter=2, tol=1e-30),
+    "nt_wide_v24": dict(n=(100, 90, 47), mode=2, pre=2, post=4, maxiter=2, tol=1e-30),
 }
 
 OPERATOR_CASES = {
@@ -64,6 +69,12 @@ OPERATOR_CASES = {
     "op_lin_mid_even": dict(n=(64, 66, 34), mode=0),
     "op_nl_mid": dict(n=(67, 50, 38), mode=1),
     "op_nt_mid": dict(n=(63, 49, 35), mode=2),
+    # wide enough for the two-sweeps-per-pass smoother: several 60-column tiles with a partial last one,
+    # partial 14-row tiles, more than one z chunk
+    "op_lin_wide": dict(n=(130, 61, 40), mode=0),
+    "op_lin_wide_even": dict(n=(120, 56, 34), mode=0),
+    "op_nl_wide": dict(n=(125, 40, 33), mode=1),
+    "op_nt_wide": dict(n=(100, 35, 20), mode=2),
 }
 
 
