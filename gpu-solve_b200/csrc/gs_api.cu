@@ -61,6 +61,7 @@ struct Level {
     size_t count;     // doubles per array
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
     bool coef_valid;
+    int gv;           // slabs: ghost planes of v that are current on each side (0..2); refreshed lazily by need_v_halo
     int pre_valid;    // vtmp == this many Jacobi sweeps of v for the current f/aux (written by the fused sweep+norm kernels)
 };
 
@@ -81,10 +82,11 @@ struct gs_handle {
     LaunchCtx cx;
     double* h_norm;  // pinned
     uint64_t launches;
-    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm;
+    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
     std::map<uint64_t, int> graphs_pre_valid;      // lev[0].pre_valid after a replay of each graph
+    std::map<uint64_t, std::vector<int>> graphs_gv;  // Level::gv after a replay of each graph
     std::map<uint64_t, uint64_t> graphs_swapped;   // bit l: level l ends a replay with v and vtmp exchanged
     std::vector<double> history;
     std::vector<EventPair> ev_used;
@@ -191,6 +193,8 @@ Partition make_partition(const gs_params& p, int world)
     P.b.resize(P.nlev);
     int min_planes = 4;
     if (const char* e = getenv("GPUSOLVE_SLAB_MIN")) min_planes = std::max(1, atoi(e));
+    double min_points = 3.0e6;
+    if (const char* e = getenv("GPUSOLVE_SLAB_MIN_POINTS")) min_points = atof(e);
     // deepest level that still gives every rank >= min_planes planes; never the last two levels
     int deepest = -1;
     if (world > 1) {
@@ -199,7 +203,10 @@ Partition make_partition(const gs_params& p, int world)
             level_dims(p, l, n);
             int Zm1 = (int)n[2] + 1;
             int blk = (Zm1 + world - 1) / world;
-            if (blk >= min_planes && (world - 1) * blk < Zm1) deepest = l;
+            // small levels are latency-bound: every rank computes them whole (no halo exchange) once the
+            // level has fewer than min_points interior points
+            const double pts = (double)n[0] * (double)n[1] * (double)n[2];
+            if (blk >= min_planes && (world - 1) * blk < Zm1 && pts >= min_points) deepest = l;
             else break;
         }
     }
@@ -275,6 +282,20 @@ int exchange_halo(gs_handle* h, int level, double* a, int depth)
     return GS_OK;
 }
 
+// make `depth` ghost planes of the level's v current (slabs only).  Operators that write v just mark the ghosts
+// stale (Level::gv = 0); the exchange happens once, two planes deep, right before the next operator that reads them.
+int need_v_halo(gs_handle* h, int level, int depth)
+{
+    if (!partitioned(h, level)) return GS_OK;
+    Level& L = h->lev[level];
+    if (L.gv >= depth) return GS_OK;
+    const int owned = L.zhi - L.zlo;
+    const int d = owned >= 2 ? 2 : depth;
+    GS(exchange_halo(h, level, L.v, d));
+    L.gv = d;
+    return GS_OK;
+}
+
 // ---- operators ------------------------------------------------------------------
 int ensure_coef(gs_handle* h, int level)
 {
@@ -306,25 +327,27 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
         iters -= L.pre_valid;
         L.pre_valid = 0;
         std::swap(L.v, L.vtmp);
-        GS(exchange_halo(h, level, L.v, 1));
+        L.gv = 0;
     }
     L.pre_valid = 0;
     const double* aux = smoother_aux(h, level, km);
+    const bool tuned = h->opt_kernels && h->canonical;
     while (iters > 0) {
         bool handled = false;
-        if (iters >= 2 && h->opt_kernels && h->canonical) {
+        GS(need_v_halo(h, level, (iters >= 2 && tuned && h->cx.tune.fuse2) ? 2 : 1));
+        if (iters >= 2 && tuned) {
             // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
-            if (partitioned(h, level) && h->cx.tune.fuse2) GS(exchange_halo(h, level, L.v, 2));
-            CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
+            if (!partitioned(h, level) || L.gv >= 2)
+                CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
             if (handled) iters -= 2;
         }
         if (!handled) {
-            if (h->opt_kernels && h->canonical) CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
+            if (tuned) CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
             if (!handled) CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, aux));
             iters--;
         }
         std::swap(L.v, L.vtmp);
-        GS(exchange_halo(h, level, L.v, 1));
+        L.gv = 0;
     }
     return GS_OK;
 }
@@ -347,6 +370,7 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     OpScope t(h, GS_OP_RESIDUAL, level);
+    GS(need_v_halo(h, level, 1));
     bool handled = false;
     if (h->opt_kernels && h->canonical)
         CU(kf_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled));
@@ -367,8 +391,8 @@ int do_norm_residual(gs_handle* h)
         OpScope t(h, GS_OP_RESIDUAL, 0);
         bool handled = false;
         const double* aux = smoother_aux(h, 0, km);
-        if (h->p.pre >= 2) {
-            if (partitioned(h, 0) && h->cx.tune.fuse2) GS(exchange_halo(h, 0, L.v, 2));
+        GS(need_v_halo(h, 0, (h->p.pre >= 2 && h->cx.tune.fuse2) ? 2 : 1));
+        if (h->p.pre >= 2 && (!partitioned(h, 0) || L.gv >= 2)) {
             CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, &handled));
             if (handled) {
                 L.pre_valid = 2;
@@ -434,7 +458,7 @@ int do_restrict_residual(gs_handle* h, int level)
     int zb = L.ib, ze = L.ie;
     if (partitioned(h, level)) {
         // the lowest owned coarse plane needs r one fine plane below the slab, which needs v two below
-        GS(exchange_halo(h, level, L.v, 2));
+        GS(need_v_halo(h, level, 2));
         if (L.zlo > 0) zb = L.ib - 1;
     }
     int km = smoother_km(h);
@@ -457,7 +481,9 @@ int do_fas_coarse_rhs(gs_handle* h, int level)
 {
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_RESTRICT, level);
+    GS(need_v_halo(h, level, 1));
     GS(do_restrict(h, level, h->lev[level].v, C.restV, C.v));
+    C.gv = 1;  // finish_coarse refreshed one ghost plane of both outputs
     CU(ks_fas_rhs(h->cx, C.pow2, C.g, C.ib, C.ie, C.k, h->so, C.restV, C.f, C.r));
     GS(exchange_halo(h, level + 1, C.f, 1));  // f changed on the owned planes only
     return GS_OK;
@@ -470,8 +496,10 @@ int do_prolong_correct(gs_handle* h, int level)
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_PROLONG, level);
     F.pre_valid = 0;
+    GS(need_v_halo(h, level + 1, 1));  // the interpolation reads one coarse plane outside the slab
     if (h->p.mode == GS_MODE_NONLINEAR) {
         CU(ks_axpy(h->cx, C.g, 0, C.g.nzl, C.v, C.restV, -1));
+        C.gv = std::min(C.gv, 1);  // restV carries one current ghost plane
     }
     // an odd number of sweeps per cycle would leave v/vtmp swapped; writing the corrected
     // field out of place in that case keeps the buffer parity (and the CUDA graph) fixed
@@ -480,7 +508,7 @@ int do_prolong_correct(gs_handle* h, int level)
     if (h->opt_kernels) CU(kt_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, &handled));
     if (!handled) CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
     if (flip) std::swap(F.v, F.vtmp);
-    GS(exchange_halo(h, level, F.v, 1));
+    F.gv = 0;
     return GS_OK;
 }
 
@@ -489,6 +517,7 @@ int zero_field(gs_handle* h, Level& L, double* a)
     L.pre_valid = false;
     OpScope t(h, GS_OP_OTHER, (int)(&L - h->lev.data()));
     CU(cudaMemsetAsync(a, 0, L.count * sizeof(double), h->stream));
+    if (a == L.v) L.gv = 2;  // ghost planes included
     return GS_OK;
 }
 
@@ -532,6 +561,10 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
+    // slabs: which ghost planes are current decides which exchanges the captured cycle contains
+    uint64_t gvs = 0;
+    for (size_t l = 0; l < h->lev.size(); l++) gvs = gvs * 3 + (uint64_t)(partitioned(h, (int)l) ? h->lev[l].gv : 0);
+    key ^= gvs * 0x9E3779B97F4A7C15ull;
     return key;
 }
 
@@ -540,7 +573,7 @@ int run_vcycle(gs_handle* h, double* norm)
     const bool need_coef = smoother_km(h) == KM_NEWTON_COEF;
     if (need_coef)
         for (size_t l = 0; l < h->lev.size(); l++) GS(ensure_coef(h, (int)l));
-    const bool graph_ok = h->opt_graph && !h->opt_timing && h->world == 1;
+    const bool graph_ok = h->opt_graph && !h->opt_timing && (h->world == 1 || h->opt_graph_multi);
     if (!graph_ok) {
         GS(enqueue_vcycle(h));
     } else {
@@ -554,6 +587,8 @@ int run_vcycle(gs_handle* h, double* norm)
             }
             const uint64_t l0 = h->launches;
             const int pre0 = h->lev[0].pre_valid;
+            std::vector<int> gv0, gv1;
+            for (auto& L : h->lev) gv0.push_back(L.gv);
             cudaGraph_t g = nullptr;
             CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             int rc = enqueue_vcycle(h);
@@ -569,6 +604,10 @@ int run_vcycle(gs_handle* h, double* norm)
             h->launches = l0;
             const int pre1 = h->lev[0].pre_valid;
             h->lev[0].pre_valid = pre0;
+            for (size_t l = 0; l < h->lev.size(); l++) {
+                gv1.push_back(h->lev[l].gv);
+                h->lev[l].gv = gv0[l];
+            }
             if (rc != GS_OK) {
                 if (g) cudaGraphDestroy(g);
                 return rc;
@@ -581,10 +620,15 @@ int run_vcycle(gs_handle* h, double* norm)
             h->graphs_launches[key] = per_cycle;
             h->graphs_pre_valid[key] = pre1;
             h->graphs_swapped[key] = swapped;
+            h->graphs_gv[key] = gv1;
         }
         CU(cudaGraphLaunch(it->second, h->stream));
         h->launches += h->graphs_launches[key];
         h->lev[0].pre_valid = h->graphs_pre_valid[key];
+        {
+            const std::vector<int>& gv1 = h->graphs_gv[key];
+            for (size_t l = 0; l < h->lev.size(); l++) h->lev[l].gv = gv1[l];
+        }
         // host-side view of the buffer parity after the cycle (the graph is keyed by the parity it starts from)
         const uint64_t swapped = h->graphs_swapped[key];
         for (size_t l = 0; l < h->lev.size(); l++)
@@ -686,6 +730,7 @@ int newton_find_error(gs_handle* h, uint64_t* inner)
     Level& L0 = h->lev[0];
     {
         OpScope t(h, GS_OP_OTHER, 0);
+        GS(need_v_halo(h, 0, 2));  // the update runs over the ghost planes too: newtonV's ghosts stay current
         CU(ks_axpy(h->cx, L0.g, 0, L0.g.nzl, L0.newtonV, L0.v, +1));  // :106-107
     }
     L0.coef_valid = false;
@@ -753,6 +798,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_graph = 1;
     h->opt_timing = 0;
     h->opt_fuse_norm = 1;
+    h->opt_graph_multi = 1;  // capture the NCCL halo exchanges of a slab V-cycle into the graph as well
     h->comm = nullptr;
     h->h_norm = nullptr;
     h->stage = nullptr;
@@ -768,6 +814,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* e = getenv("GPUSOLVE_KERNELS")) h->opt_kernels = atoi(e) != 0;
     if (const char* e = getenv("GPUSOLVE_GRAPH")) h->opt_graph = atoi(e) != 0;
     if (const char* e = getenv("GPUSOLVE_FUSE_NORM")) h->opt_fuse_norm = atoi(e) != 0;
+    if (const char* e = getenv("GPUSOLVE_GRAPH_MULTI")) h->opt_graph_multi = atoi(e) != 0;
 
     Partition part = make_partition(*p, world);
     h->replicated_from = part.replicated_from;
@@ -1086,7 +1133,8 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
         if (field == GS_FIELD_V)  // keep the halo of both ping-pong buffers identical
             CU(cudaMemcpyAsync(L.vtmp, L.v, L.count * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
         CU(cudaStreamSynchronize(h->stream));
-        L.pre_valid = false;
+        L.pre_valid = 0;
+        if (field == GS_FIELD_V) L.gv = 2;  // every rank received its ghost planes from the dense array
         if (field == GS_FIELD_NEWTONV) L.coef_valid = false;
         if (field == GS_FIELD_NEWTONF) h->newton_begun = true;
     }
@@ -1147,8 +1195,12 @@ int gs_restrict(gs_handle* h, int level, int src_field, int dst_field)
     double** d = field_ptr(h, level + 1, dst_field);
     if (!s || !*s || !d || !*d) return fail(GS_EINVAL, "field %d/%d not available in mode %d", src_field, dst_field, h->p.mode);
     OpScope t(h, GS_OP_RESTRICT, level);
-    if (partitioned(h, level)) GS(exchange_halo(h, level, *s, 1));
+    if (partitioned(h, level)) {
+        if (*s == h->lev[level].v) GS(need_v_halo(h, level, 1));
+        else GS(exchange_halo(h, level, *s, 1));
+    }
     GS(do_restrict(h, level, *s, *d, nullptr));
+    if (*d == h->lev[level + 1].v) h->lev[level + 1].gv = 1;
     if (dst_field == GS_FIELD_NEWTONV) h->lev[level + 1].coef_valid = false;
     return GS_OK;
 }
