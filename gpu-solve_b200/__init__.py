@@ -110,6 +110,7 @@ SIGNATURES = {
     "gs_reset_timing": (_i, [_vp]),
     "gs_get_timing": (_i, [_vp, C.POINTER(C.c_double * 5), C.POINTER(_u64 * 5)]),
     "gs_get_level_timing": (_i, [_vp, _i, C.POINTER(C.c_double * 5), C.POINTER(_u64 * 5)]),
+    "gs_get_level_sweeps": (_i, [_vp, _i, C.POINTER(_u64)]),
     "gs_launch_count": (_u64, [_vp]),
     "gs_set_option": (_i, [_vp, C.c_char_p, C.c_int64]),
     "gs_stream": (_vp, [_vp]),
@@ -277,6 +278,11 @@ class GpuSolve:
         ms, n = (C.c_double * 5)(), (C.c_uint64 * 5)()
         _check(self.lib.gs_get_level_timing(self.h, level, C.byref(ms), C.byref(n)))
         return {OPS[i]: (ms[i], n[i]) for i in range(5)}
+
+    def level_sweeps(self, level):
+        n = C.c_uint64()
+        _check(self.lib.gs_get_level_sweeps(self.h, level, C.byref(n)))
+        return n.value
 
     @property
     def launches(self):

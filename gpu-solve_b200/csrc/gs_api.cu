@@ -95,6 +95,7 @@ struct gs_handle {
     uint64_t op_launches[GS_OP_COUNT];
     std::vector<double> lvl_ms;          // [level][op]
     std::vector<uint64_t> lvl_launches;  // [level][op]
+    std::vector<uint64_t> lvl_sweeps;    // [level] Jacobi sweeps run by the GS_OP_SMOOTH launches
     GsComm* comm;
     int replicated_from;
     double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
@@ -339,12 +340,16 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
             // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
             if (!partitioned(h, level) || L.gv >= 2)
                 CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
-            if (handled) iters -= 2;
+            if (handled) {
+                iters -= 2;
+                h->lvl_sweeps[level] += 2;
+            }
         }
         if (!handled) {
             if (tuned) CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
             if (!handled) CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, aux));
             iters--;
+            h->lvl_sweeps[level]++;
         }
         std::swap(L.v, L.vtmp);
         L.gv = 0;
@@ -822,6 +827,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->lev.resize(nlev);
     h->lvl_ms.assign((size_t)nlev * GS_OP_COUNT, 0.0);
     h->lvl_launches.assign((size_t)nlev * GS_OP_COUNT, 0);
+    h->lvl_sweeps.assign((size_t)nlev, 0);
     const int ghost = 2;
     size_t max_blocks = 1;
     int rc = GS_OK;
@@ -1327,6 +1333,7 @@ int gs_reset_timing(gs_handle* h)
     memset(h->op_launches, 0, sizeof h->op_launches);
     std::fill(h->lvl_ms.begin(), h->lvl_ms.end(), 0.0);
     std::fill(h->lvl_launches.begin(), h->lvl_launches.end(), 0);
+    std::fill(h->lvl_sweeps.begin(), h->lvl_sweeps.end(), 0);
     return GS_OK;
 }
 
@@ -1354,6 +1361,13 @@ int gs_get_level_timing(gs_handle* h, int level, double ms[GS_OP_COUNT], uint64_
         if (ms) ms[i] = h->lvl_ms[(size_t)level * GS_OP_COUNT + i];
         if (launches) launches[i] = h->lvl_launches[(size_t)level * GS_OP_COUNT + i];
     }
+    return GS_OK;
+}
+
+int gs_get_level_sweeps(gs_handle* h, int level, uint64_t* sweeps)
+{
+    GS(check_level(h, level));
+    if (sweeps) *sweeps = h->lvl_sweeps[level];
     return GS_OK;
 }
 

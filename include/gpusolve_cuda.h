@@ -175,13 +175,20 @@ int  gs_reset_timing(gs_handle* h);
 int  gs_get_timing(gs_handle* h, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT]);
 /* the same, for one level (the level an operator is called ON: restriction from l to l+1 counts on l) */
 int  gs_get_level_timing(gs_handle* h, int level, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT]);
+/* Jacobi sweeps applied to `level` by its GS_OP_SMOOTH launches since gs_reset_timing (a two-sweeps-per-pass
+ * launch of kernels_fused.cu counts 2; sweeps produced together with a residual norm count under GS_OP_RESIDUAL) */
+int  gs_get_level_sweeps(gs_handle* h, int level, uint64_t* sweeps);
 /* total kernels launched by this handle since creation */
 uint64_t gs_launch_count(const gs_handle* h);
 /* options: "kernels" = 0 simple one-thread-per-point kernels, 1 tuned (default);
  *          "graph"   = 0/1 capture the V-cycle in a CUDA graph (default 1);
  *          "timing"  = 0/1 per-operator CUDA events (default 0, disables graph);
- *          "smooth_variant", "zchunk", "fast_min_n" = kernel tuning knobs
- *          (gpu-solve_b200/csrc/kernels_fast.cu), also GPUSOLVE_* environment */
+ *          "smooth_variant", "zchunk", "fast_min_n", "rr_variant" = kernel tuning knobs
+ *          (gpu-solve_b200/csrc/kernels_fast.cu, kernels_transfer.cu);
+ *          "fuse2" = 0 one Jacobi sweep per pass, 1..3 two sweeps per pass (tile variant,
+ *          kernels_fused.cu; default 1), "fuse2_min_n", "zchunk2" its knobs;
+ *          "fuse_norm" = 0/1 produce the next pre-smoothing sweep(s) together with the
+ *          V-cycle's final residual norm (default 1); also GPUSOLVE_* environment */
 int  gs_set_option(gs_handle* h, const char* name, int64_t value);
 /* the CUDA stream all work of this handle is issued on (a cudaStream_t) */
 void* gs_stream(gs_handle* h);

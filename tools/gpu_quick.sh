@@ -4,11 +4,11 @@
 tag=${1:-q}; kexpr=${2:-}
 out=gpurun_out; mkdir -p $out
 if [ -n "$kexpr" ]; then
-  timeout 1500 python -m pytest tests -m gpu -x -q -k "$kexpr" > $out/${tag}_pytest.log 2>&1
+  timeout 400 python -m pytest tests -m gpu -x -q -k "$kexpr" > $out/${tag}_pytest.log 2>&1
 else
-  timeout 1500 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1
+  timeout 400 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest.log 2>&1
 fi
 echo "pytest exit $?" >> $out/${tag}_pytest.log
-timeout 600 python tools/profile_levels.py --out $out/${tag}_levels.json > $out/${tag}_levels.txt 2>&1
-timeout 600 python bench.py --no-cpu > $out/${tag}_bench.json 2> $out/${tag}_bench.err
+timeout 120 python tools/profile_levels.py --out $out/${tag}_levels.json > $out/${tag}_levels.txt 2>&1
+timeout 300 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err
 echo done
