@@ -54,7 +54,8 @@ struct Level {
     Geom g;
     double h;
     PointK k;
-    bool pow2;
+    bool pow2, unit;
+    int ar;  // arithmetic flags of the tuned kernels (gs_device.cuh AR_*), same bits either way
     int zlo, zhi;     // owned GLOBAL planes [zlo, zhi) (both physical halo planes belong to the end ranks)
     int ib, ie;       // LOCAL plane range [ib, ie) of owned interior planes
     bool replicated;  // whole level held (and computed) by every rank
@@ -339,14 +340,14 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
         if (iters >= 2 && tuned) {
             // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
             if (!partitioned(h, level) || L.gv >= 2)
-                CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
+                CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
             if (handled) {
                 iters -= 2;
                 h->lvl_sweeps[level] += 2;
             }
         }
         if (!handled) {
-            if (tuned) CU(kf_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
+            if (tuned) CU(kf_smooth(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
             if (!handled) CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, aux));
             iters--;
             h->lvl_sweeps[level]++;
@@ -378,7 +379,7 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     GS(need_v_halo(h, level, 1));
     bool handled = false;
     if (h->opt_kernels && h->canonical)
-        CU(kf_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled));
+        CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled));
     if (!handled)
         CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
     return GS_OK;
@@ -398,13 +399,13 @@ int do_norm_residual(gs_handle* h)
         const double* aux = smoother_aux(h, 0, km);
         GS(need_v_halo(h, 0, (h->p.pre >= 2 && h->cx.tune.fuse2) ? 2 : 1));
         if (h->p.pre >= 2 && (!partitioned(h, 0) || L.gv >= 2)) {
-            CU(kx_smooth2(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, &handled));
+            CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, &handled));
             if (handled) {
                 L.pre_valid = 2;
                 return GS_OK;
             }
         }
-        CU(kf_smooth_norm(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
+        CU(kf_smooth_norm(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
         if (handled) {
             L.pre_valid = 1;
             return GS_OK;
@@ -473,7 +474,7 @@ int do_restrict_residual(gs_handle* h, int level)
         int czb, cze;
         coarse_range(h, level, &czb, &cze);
         bool handled = false;
-        CU(kt_resid_restrict(h->cx, km, L.pow2, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
+        CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
         if (handled) return finish_coarse(h, level, C.f);
     }
     CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
@@ -564,6 +565,8 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->lev[0].pre_valid & 3) << 15;
     key ^= (uint64_t)(h->cx.tune.fuse2 & 7) << 12;
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
+    key ^= (uint64_t)(h->lev[0].ar & 3) << 10;
+    key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     // slabs: which ghost planes are current decides which exchanges the captured cycle contains
@@ -867,6 +870,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
         k.hh = L.h * L.h;
         L.pow2 = is_pow2(k.hh);
         k.inv_hh = L.pow2 ? 1.0 / k.hh : 0.0;
+        bool unit = true;
+        for (int i = 1; i < 7; i++) unit = unit && p->stencil_val[i] == -1.0;
+        L.unit = unit;
+        L.ar = (L.pow2 ? 1 : 0) | (unit ? 2 : 0);
         k.alpha = (L.h * L.h) / p->stencil_val[0];   // src/cpu/CpuSolver.cpp:145
         k.preFac = p->stencil_val[0] / (L.h * L.h);  // :144
         k.omega = p->omega;
@@ -911,6 +918,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->cx.tune.fuse2 = 1;
     h->cx.tune.fuse2_min_n = 96;
     h->cx.tune.zchunk2 = 128;
+    h->cx.tune.wave = 1;
+    if (const char* ev = getenv("GPUSOLVE_WAVE")) h->cx.tune.wave = atoi(ev) != 0;
     if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(3, atoi(ev)));
     if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = atoi(ev) != 0;
     e = kf_prepare();
@@ -1400,7 +1409,10 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
-    else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
+    else if (n == "wave") h->cx.tune.wave = value != 0;
+    else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
+        for (auto& L : h->lev) L.ar = (L.pow2 ? 1 : 0) | ((L.unit && value != 0) ? 2 : 0);
+    } else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
     else if (n == "fuse2") {
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(3, value));
         h->lev[0].pre_valid = 0;

@@ -16,6 +16,9 @@ bool gs_tensor_map(const double* base, const Geom& g, int bw, int bh, CUtensorMa
 // planes per CTA of a z-marching kernel: long chunks (each re-reads its rim planes), but short
 // enough that small levels still put several CTAs on every SM
 int gs_pick_zchunk(const LaunchCtx& cx, int tiles, int planes, int max_chunk);
+// the same with wave quantisation taken into account (tune.wave): see kernels_fast.cu
+int gs_pick_zchunk_waves(const LaunchCtx& cx, int tiles, int planes, int ctas_per_sm, int overhead, int min_chunk, int max_chunk,
+                         bool even);
 
 // ---------------------------------------------------------------------------------
 // point arithmetic
@@ -23,10 +26,31 @@ int gs_pick_zchunk(const LaunchCtx& cx, int tiles, int planes, int max_chunk);
 // s = sum_i c_i v(p+o_i) (already accumulated, i ascending: src/cpu/CpuSolver.cpp:56-60)
 // -> r = f - (s/(h*h) + NL), and the Jacobi denominator (modes 1..3)
 // src/cpu/CpuSolver.cpp:61-74 (residual) and :161-171 (denominator)
-template <int KM, bool POW2>
+// AR = arithmetic flags of a level, chosen on the host (gs_api.cu create_impl); every value gives the same bits:
+//   AR_POW2  h*h is a power of two: s * (1/hh) == s / hh exactly
+//   AR_UNIT  the six off-centre stencil values are exactly -1: s + (-1.0)*v == s - v exactly (IEEE: a - b is
+//            a + (-b), and -1.0*v is v with the sign flipped), so the six multiplies are dropped
+// Instantiated combinations: 0 (general), AR_POW2, AR_POW2|AR_UNIT; a level with unit taps but a non-power-of-two
+// h*h runs the general code (its fp64 divide dominates anyway).
+enum { AR_POW2 = 1, AR_UNIT = 2 };
+#define AR_SWITCH(ar, STMT)                                  \
+    do {                                                     \
+        if ((ar) == (AR_POW2 | AR_UNIT)) {                   \
+            constexpr int ARV = AR_POW2 | AR_UNIT;           \
+            STMT;                                            \
+        } else if ((ar) & AR_POW2) {                         \
+            constexpr int ARV = AR_POW2;                     \
+            STMT;                                            \
+        } else {                                             \
+            constexpr int ARV = 0;                           \
+            STMT;                                            \
+        }                                                    \
+    } while (0)
+
+template <int KM, int AR>
 __device__ __forceinline__ double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
 {
-    s = POW2 ? s * k.inv_hh : s / k.hh;
+    s = (AR & AR_POW2) ? s * k.inv_hh : s / k.hh;
     den = 0.0;
     if (KM == KM_NONLINEAR) {
         double ex = exp(vc);
@@ -56,10 +80,20 @@ __device__ __forceinline__ double jacobi_update(double vc, double r, double den,
 }
 
 // canonical tap order C,+x,-x,+y,-y,+z,-z (config order of the axis-aligned stencil)
+template <int AR>
 __device__ __forceinline__ double canon_tap_sum(double C, double E, double W, double N, double S, double U, double D, const PointK& k)
 {
     double s = 0.0;
     s += k.c[0] * C;
+    if (AR & AR_UNIT) {
+        s -= E;
+        s -= W;
+        s -= N;
+        s -= S;
+        s -= U;
+        s -= D;
+        return s;
+    }
     s += k.c[1] * E;
     s += k.c[2] * W;
     s += k.c[3] * N;
@@ -69,11 +103,11 @@ __device__ __forceinline__ double canon_tap_sum(double C, double E, double W, do
     return s;
 }
 
-template <int KM, bool POW2>
+template <int KM, int AR>
 __device__ __forceinline__ double canon_residual(double C, double E, double W, double N, double S, double U, double D, double fv,
                                                  double aux, const PointK& k, double& den)
 {
-    return finish_residual<KM, POW2>(canon_tap_sum(C, E, W, N, S, U, D, k), C, fv, aux, k, den);
+    return finish_residual<KM, AR>(canon_tap_sum<AR>(C, E, W, N, S, U, D, k), C, fv, aux, k, den);
 }
 
 // ---------------------------------------------------------------------------------

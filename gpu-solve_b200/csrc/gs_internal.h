@@ -67,6 +67,7 @@ struct Tune {
     int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1.. = tile variant + 1
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
     int zchunk2;         // planes per CTA of the two-sweep kernel
+    int wave;            // 1: size z chunks so the grid fills whole waves of resident CTAs (gs_pick_zchunk_waves)
 };
 
 struct LaunchCtx {
@@ -108,25 +109,25 @@ cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, 
 bool kf_available();
 // one-time per-process setup (dynamic shared memory attributes); call outside stream capture
 cudaError_t kf_prepare();
-cudaError_t kf_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+cudaError_t kf_smooth(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
                       const double* vin, double* vout, const double* f, const double* aux, bool* handled);
 // r = f - A(v) (stored if r != nullptr) and sum of squares -> cx.norm.result
-cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+cudaError_t kf_residual(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
                         const double* v, const double* f, const double* aux, double* r, bool* handled);
 // vout = sweep(vin) and sum of squares of the residual of vin -> cx.norm.result
-cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
                            const double* vin, double* vout, const double* f, const double* aux, bool* handled);
 
 // ---- kernels_fused.cu: two Jacobi sweeps per pass (temporal blocking, bit-identical to two single sweeps) ----
 cudaError_t kx_prepare();
 // vout = S(S(vin)) on local planes [zb, ze); needs two valid planes of vin outside the range.  with_norm: also
 // sum of squares of the residual of vin -> cx.norm.result
-cudaError_t kx_smooth2(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
                        const double* vin, double* vout, const double* f, const double* aux, bool with_norm, bool* handled);
 
 // ---- kernels_transfer.cu: tuned grid-transfer kernels (canonical stencil) ----
 cudaError_t kt_prepare();
 cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
                                double* vout, const double* coarse, bool* handled);
-cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, bool pow2, const Geom& gf, const Geom& gc, int zcb, int zce,
+cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
                               const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled);

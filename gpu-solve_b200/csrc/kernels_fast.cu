@@ -82,6 +82,35 @@ int gs_pick_zchunk(const LaunchCtx& cx, int tiles, int planes, int max_chunk)
 }
 
 
+// Wave-aware variant: a z-marching CTA costs about (chunk + overhead) plane-times — `overhead` = rim planes it
+// re-reads / recomputes plus the pipeline fill — and the grid runs in ceil(CTAs / resident slots) waves, the
+// last of which leaves SMs idle when it is partial.  Choose the chunk count that minimises waves x CTA cost, so the
+// grid is (close to) a whole multiple of sm_count x resident CTAs per SM.
+int gs_pick_zchunk_waves(const LaunchCtx& cx, int tiles, int planes, int ctas_per_sm, int overhead, int min_chunk, int max_chunk,
+                         bool even)
+{
+    if (planes <= 0) return 1;
+    const long slots = (long)cx.sm_count * (ctas_per_sm > 0 ? ctas_per_sm : 1);
+    if (max_chunk > planes) max_chunk = planes;
+    if (min_chunk > max_chunk) min_chunk = max_chunk;
+    long best_cost = -1;
+    int best_chunk = max_chunk;
+    for (int n = 1; n <= planes; n++) {
+        int chunk = (planes + n - 1) / n;
+        if (even) chunk += chunk & 1;
+        if (chunk > max_chunk) continue;
+        if (chunk < min_chunk) break;
+        const long nch = (planes + chunk - 1) / chunk;
+        const long waves = (tiles * nch + slots - 1) / slots;
+        const long cost = waves * (chunk + overhead);
+        if (best_cost < 0 || cost < best_cost) {
+            best_cost = cost;
+            best_chunk = chunk;
+        }
+    }
+    return best_chunk;
+}
+
 bool kf_available() { return encode_fn() != nullptr; }
 
 namespace {
@@ -99,19 +128,19 @@ struct FastP {
     NormBuf nb;    // OP_RESID
 };
 
-template <int KM, bool POW2>
+template <int KM, int AR>
 __device__ __forceinline__ double point_update(double C, double E, double W, double N, double S, double U, double D, double fv,
                                                double aux, const PointK& k)
 {
     double den;
-    const double r = canon_residual<KM, POW2>(C, E, W, N, S, U, D, fv, aux, k, den);
+    const double r = canon_residual<KM, AR>(C, E, W, N, S, U, D, fv, aux, k, den);
     return jacobi_update<KM>(C, r, den, k);
 }
 
 // ---------------------------------------------------------------------------------
 // variant 1: register-queue z-march, in-plane neighbours through L1
 // ---------------------------------------------------------------------------------
-template <int KM, bool POW2, int BX, int BY>
+template <int KM, int AR, int BX, int BY>
 __global__ void __launch_bounds__(BX* BY) smooth_zmarch(FastP p)
 {
     const int x = blockIdx.x * BX + threadIdx.x + 1;
@@ -129,7 +158,7 @@ __global__ void __launch_bounds__(BX* BY) smooth_zmarch(FastP p)
         const double fv = p.f[c];
         const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
         const double E = v[c + 1], W = v[c - 1], N = v[c + pitch], S = v[c - pitch];
-        p.vout[c] = point_update<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k);
+        p.vout[c] = point_update<KM, AR>(C, E, W, N, S, U, D, fv, aux, p.k);
         D = C;
         C = U;
         c += plane;
@@ -154,7 +183,7 @@ struct TmaCfg {
     static constexpr int THREADS = CONSUMERS + 32;
 };
 
-template <int KM, bool POW2, int OP, int TX, int TY, int NSTAGE>
+template <int KM, int AR, int OP, int TX, int TY, int NSTAGE>
 __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant__ CUtensorMap map_v,
                                                             const __grid_constant__ CUtensorMap map_f, FastP p)
 {
@@ -225,18 +254,18 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
         __syncwarp();
         if (lane0) mbar_arrive(&empty[q % NSTAGE]);
         if (OP == OP_SMOOTH) {
-            const double nv = point_update<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k);
+            const double nv = point_update<KM, AR>(C, E, W, N, S, U, D, fv, aux, p.k);
             if (live) p.vout[c] = nv;
         } else if (OP == OP_SMOOTH_NORM) {
             double den;
-            const double r = canon_residual<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k, den);
+            const double r = canon_residual<KM, AR>(C, E, W, N, S, U, D, fv, aux, p.k, den);
             if (live) {
                 p.vout[c] = jacobi_update<KM>(C, r, den, p.k);
                 sq += r * r;
             }
         } else {
             double den;
-            const double r = canon_residual<KM, POW2>(C, E, W, N, S, U, D, fv, aux, p.k, den);
+            const double r = canon_residual<KM, AR>(C, E, W, N, S, U, D, fv, aux, p.k, den);
             if (live) {
                 if (p.vout) p.vout[c] = r;
                 sq += r * r;  // per-thread running sum in plane order: deterministic
@@ -257,37 +286,42 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
 // ---------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------
-template <int KM, bool POW2, int OP, int TX, int TY, int NSTAGE>
+template <int KM, int AR, int OP, int TX, int TY, int NSTAGE>
 cudaError_t launch_tma(const LaunchCtx& cx, FastP p, bool* handled)
 {
     using Cfg = TmaCfg<TX, TY, NSTAGE>;
     static bool prepared = false;  // raise the dynamic shared memory limit once per instantiation (outside stream capture:
-    if (!prepared) {               // kf_prepare() instantiates every kernel the dispatchers can reach)
-        cudaError_t e = cudaFuncSetAttribute(stencil_tma<KM, POW2, OP, TX, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    static int occ = 1;            // kf_prepare() instantiates every kernel the dispatchers can reach)
+    if (!prepared) {
+        cudaError_t e = cudaFuncSetAttribute(stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
+        if (e == cudaSuccess)
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
         if (e != cudaSuccess) return e;
         prepared = true;
     }
     if (!p.vin) return cudaSuccess;  // preparation call
     CUtensorMap mv, mf;
     if (!gs_tensor_map(p.vin, p.g, Cfg::VW, Cfg::VH, &mv) || !gs_tensor_map(p.f, p.g, TX, TY, &mf)) return cudaSuccess;  // not handled
-    p.zchunk = gs_pick_zchunk(cx, ((p.g.nx + TX - 1) / TX) * ((p.g.ny + TY - 1) / TY), p.ze - p.zb, p.zchunk);
+    const int tiles = ((p.g.nx + TX - 1) / TX) * ((p.g.ny + TY - 1) / TY);
+    if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tiles, p.ze - p.zb, occ, 2 + NSTAGE / 2, 8, p.zchunk, false);
+    else p.zchunk = gs_pick_zchunk(cx, tiles, p.ze - p.zb, p.zchunk);
     const int nzc = (p.ze - p.zb + p.zchunk - 1) / p.zchunk;
     dim3 grid((p.g.nx + TX - 1) / TX, (p.g.ny + TY - 1) / TY, nzc);
     if (OP != OP_SMOOTH && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;  // not handled
-    stencil_tma<KM, POW2, OP, TX, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    stencil_tma<KM, AR, OP, TX, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
     *handled = true;
     return cudaGetLastError();
 }
 
-template <int KM, bool POW2, int BX, int BY>
+template <int KM, int AR, int BX, int BY>
 cudaError_t launch_zmarch(const LaunchCtx& cx, FastP p, bool* handled)
 {
     if (!p.vin) return cudaSuccess;
     p.zchunk = gs_pick_zchunk(cx, ((p.g.nx + BX - 1) / BX) * ((p.g.ny + BY - 1) / BY), p.ze - p.zb, p.zchunk);
     const int nzc = (p.ze - p.zb + p.zchunk - 1) / p.zchunk;
     dim3 grid((p.g.nx + BX - 1) / BX, (p.g.ny + BY - 1) / BY, nzc);
-    smooth_zmarch<KM, POW2, BX, BY><<<grid, dim3(BX, BY), 0, cx.stream>>>(p);
+    smooth_zmarch<KM, AR, BX, BY><<<grid, dim3(BX, BY), 0, cx.stream>>>(p);
     *handled = true;
     return cudaGetLastError();
 }
@@ -297,28 +331,28 @@ cudaError_t launch_zmarch(const LaunchCtx& cx, FastP p, bool* handled)
 // id, BX, BY
 #define ZMARCH_VARIANTS(X) X(1, 64, 4) X(13, 64, 8)
 
-template <int KM, bool POW2>
+template <int KM, int AR>
 cudaError_t dispatch_smooth(const LaunchCtx& cx, const FastP& p, int variant, bool* handled)
 {
     switch (variant) {
 #define X(id, bx, by) \
-    case id: return launch_zmarch<KM, POW2, bx, by>(cx, p, handled);
+    case id: return launch_zmarch<KM, AR, bx, by>(cx, p, handled);
         ZMARCH_VARIANTS(X)
 #undef X
 #define X(id, tx, ty, ns) \
-    case id: return launch_tma<KM, POW2, OP_SMOOTH, tx, ty, ns>(cx, p, handled);
+    case id: return launch_tma<KM, AR, OP_SMOOTH, tx, ty, ns>(cx, p, handled);
         TMA_VARIANTS(X)
 #undef X
     default: return cudaSuccess;  // not handled: caller uses the simple kernel
     }
 }
 
-template <int KM, bool POW2, int OP>
+template <int KM, int AR, int OP>
 cudaError_t dispatch_resid(const LaunchCtx& cx, const FastP& p, bool* handled)
 {
     // wide tiles on big levels, the narrow tile where 128 columns would leave most of a CTA idle
-    if (p.g.nx >= 96) return launch_tma<KM, POW2, OP, 128, 4, 4>(cx, p, handled);
-    return launch_tma<KM, POW2, OP, 64, 4, 4>(cx, p, handled);
+    if (p.g.nx >= 96) return launch_tma<KM, AR, OP, 128, 4, 4>(cx, p, handled);
+    return launch_tma<KM, AR, OP, 64, 4, 4>(cx, p, handled);
 }
 
 // run `what` for every (mode, pow2) instantiation
@@ -334,7 +368,7 @@ cudaError_t dispatch_resid(const LaunchCtx& cx, const FastP& p, bool* handled)
 
 }  // namespace
 
-cudaError_t kf_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
+cudaError_t kf_smooth(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
                       double* vout, const double* f, const double* aux, bool* handled)
 {
     *handled = false;
@@ -349,14 +383,14 @@ cudaError_t kf_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int
     int variant = cx.tune.smooth_variant;
     if (vin && variant == 22 && g.nx < 96) variant = 2;
     cudaError_t e = cudaSuccess;
-#define CALL(KMV) e = pow2 ? dispatch_smooth<KMV, true>(cx, p, variant, handled) : dispatch_smooth<KMV, false>(cx, p, variant, handled)
+#define CALL(KMV) AR_SWITCH(ar, e = (dispatch_smooth<KMV, ARV>(cx, p, variant, handled)))
     FOR_ALL_KM(CALL);
 #undef CALL
     if (e == cudaSuccess && *handled && cx.launches) ++*cx.launches;
     return e;
 }
 
-cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k, const double* v,
+cudaError_t kf_residual(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* v,
                         const double* f, const double* aux, double* r, bool* handled)
 {
     *handled = false;
@@ -368,7 +402,7 @@ cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
     p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
     if (v && p.zchunk > ze - zb) p.zchunk = ze - zb;
     cudaError_t e = cudaSuccess;
-#define CALL(KMV) e = pow2 ? dispatch_resid<KMV, true, OP_RESID>(cx, p, handled) : dispatch_resid<KMV, false, OP_RESID>(cx, p, handled)
+#define CALL(KMV) AR_SWITCH(ar, e = (dispatch_resid<KMV, ARV, OP_RESID>(cx, p, handled)))
     FOR_ALL_KM(CALL);
 #undef CALL
     if (e == cudaSuccess && *handled && cx.launches) ++*cx.launches;
@@ -377,7 +411,7 @@ cudaError_t kf_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
 
 // vout = one Jacobi sweep of vin, and sum of squares of the residual of vin -> cx.norm.result: the residual the
 // V-cycle returns (src/cpu/CpuSolver.cpp:138) is the one the next cycle's first pre-smoothing sweep starts from (:88)
-cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
                            const double* vin, double* vout, const double* f, const double* aux, bool* handled)
 {
     *handled = false;
@@ -389,8 +423,7 @@ cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, bool pow2, const Geom& g
     p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
     if (vin && p.zchunk > ze - zb) p.zchunk = ze - zb;
     cudaError_t e = cudaSuccess;
-#define CALL(KMV) \
-    e = pow2 ? dispatch_resid<KMV, true, OP_SMOOTH_NORM>(cx, p, handled) : dispatch_resid<KMV, false, OP_SMOOTH_NORM>(cx, p, handled)
+#define CALL(KMV) AR_SWITCH(ar, e = (dispatch_resid<KMV, ARV, OP_SMOOTH_NORM>(cx, p, handled)))
     FOR_ALL_KM(CALL);
 #undef CALL
     if (e == cudaSuccess && *handled && cx.launches) ++*cx.launches;
@@ -410,15 +443,15 @@ cudaError_t kf_prepare()
     cudaError_t e = cudaSuccess;
     const int variants[] = {1, 13, 2, 21, 22};
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
-        for (int pw = 0; pw < 2 && e == cudaSuccess; pw++) {
+        for (int pw = 0; pw < 4 && e == cudaSuccess; pw++) {
             for (int var : variants) {
                 cx.tune.smooth_variant = var;
-                if (e == cudaSuccess) e = kf_smooth(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+                if (e == cudaSuccess) e = kf_smooth(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
             }
             for (int nx : {64, 128}) {
                 g.nx = nx;
-                if (e == cudaSuccess) e = kf_residual(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
-                if (e == cudaSuccess) e = kf_smooth_norm(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+                if (e == cudaSuccess) e = kf_residual(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+                if (e == cudaSuccess) e = kf_smooth_norm(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
             }
             g.nx = 0;
         }

@@ -54,7 +54,7 @@ struct S2Cfg {
     static_assert(NCONS % 32 == 0 && NCONS <= 992, "consumer threads");
 };
 
-template <int KM, bool POW2, bool NORM, int TY, int NSTAGE>
+template <int KM, int AR, bool NORM, int TY, int NSTAGE>
 __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(const __grid_constant__ CUtensorMap map_v,
                                                                            const __grid_constant__ CUtensorMap map_f, Fused2P p)
 {
@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
 
         // ---- first sweep on plane q ----
         double dena, denb;
-        const double ra = canon_residual<KM, POW2>(Ca, Ea, Wa, Cb, Sa, Ua, Da, fa, xa, p.k, dena);
-        const double rb = canon_residual<KM, POW2>(Cb, Eb, Wb, Nb, Ca, Ub, Db, fb, xb, p.k, denb);
+        const double ra = canon_residual<KM, AR>(Ca, Ea, Wa, Cb, Sa, Ua, Da, fa, xa, p.k, dena);
+        const double rb = canon_residual<KM, AR>(Cb, Eb, Wb, Nb, Ca, Ub, Db, fb, xb, p.k, denb);
         double U1a = jacobi_update<KM>(Ca, ra, dena, p.k);
         double U1b = jacobi_update<KM>(Cb, rb, denb, p.k);
         U1a = (a1 && zok) ? U1a : 0.0;
@@ -178,9 +178,9 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
             const double E1a = sr[is + eo], W1a = sr[is - wo], S1a = sr[isS];
             const double E1b = sr[is + BW + eo], W1b = sr[is + BW - wo], N1b = sr[isN];
             double d2;
-            const double r2a = canon_residual<KM, POW2>(C1a, E1a, W1a, C1b, S1a, U1a, D1a, fpa, xpa, p.k, d2);
+            const double r2a = canon_residual<KM, AR>(C1a, E1a, W1a, C1b, S1a, U1a, D1a, fpa, xpa, p.k, d2);
             const double na = jacobi_update<KM>(C1a, r2a, d2, p.k);
-            const double r2b = canon_residual<KM, POW2>(C1b, E1b, W1b, N1b, C1a, U1b, D1b, fpb, xpb, p.k, d2);
+            const double r2b = canon_residual<KM, AR>(C1b, E1b, W1b, N1b, C1a, U1b, D1b, fpb, xpb, p.k, d2);
             const double nb = jacobi_update<KM>(C1b, r2b, d2, p.k);
             if (oa) p.vout[ca - plane] = na;
             if (ob) p.vout[ca - plane + ab] = nb;
@@ -197,14 +197,17 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
     }
 }
 
-template <int KM, bool POW2, bool NORM, int TY, int NSTAGE>
+template <int KM, int AR, bool NORM, int TY, int NSTAGE>
 cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
 {
     using Cfg = S2Cfg<TY, NSTAGE>;
     static bool prepared = false;
+    static int occ = 1;
     if (!prepared) {
-        cudaError_t e = cudaFuncSetAttribute(smooth2_tma<KM, POW2, NORM, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(smooth2_tma<KM, AR, NORM, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
+        if (e == cudaSuccess)
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smooth2_tma<KM, AR, NORM, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
         if (e != cudaSuccess) return e;
         prepared = true;
     }
@@ -218,21 +221,23 @@ cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
     int chunk = (planes + want - 1) / want;
     chunk = max(chunk, min(planes, 32));
     chunk = min(chunk, p.zchunk);
+    // four rim planes re-read, two first-sweep planes recomputed, pipeline fill
+    if (cx.tune.wave) chunk = gs_pick_zchunk_waves(cx, tx * ty, planes, occ, 6, min(planes, 16), p.zchunk, false);
     p.zchunk = chunk;
     dim3 grid(tx, ty, (planes + chunk - 1) / chunk);
     if (NORM && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;
-    smooth2_tma<KM, POW2, NORM, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    smooth2_tma<KM, AR, NORM, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
     *handled = true;
     return cudaGetLastError();
 }
 
-template <int KM, bool POW2, bool NORM>
+template <int KM, int AR, bool NORM>
 cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool* handled)
 {
     switch (variant) {
-    case 1: return launch_s2<KM, POW2, NORM, 14, 3>(cx, p, handled);
-    case 2: return launch_s2<KM, POW2, NORM, 22, 3>(cx, p, handled);
-    default: return launch_s2<KM, POW2, NORM, 14, 4>(cx, p, handled);
+    case 1: return launch_s2<KM, AR, NORM, 14, 3>(cx, p, handled);
+    case 2: return launch_s2<KM, AR, NORM, 22, 3>(cx, p, handled);
+    default: return launch_s2<KM, AR, NORM, 14, 4>(cx, p, handled);
     }
 }
 
@@ -240,7 +245,7 @@ cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool
 
 // vout = S(S(vin)); with_norm: also sum r(vin)^2 -> cx.norm.result.  The level must hold two valid
 // planes of vin and one of f (and aux) outside [zb, ze).
-cudaError_t kx_smooth2(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
+cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
                        double* vout, const double* f, const double* aux, bool with_norm, bool* handled)
 {
     *handled = false;
@@ -253,9 +258,9 @@ cudaError_t kx_smooth2(const LaunchCtx& cx, int km, bool pow2, const Geom& g, in
     const int lo = vin ? cx.tune.fuse2 - 1 : 0, hi = vin ? cx.tune.fuse2 - 1 : 2;
     cudaError_t e = cudaSuccess;
     for (int var = lo; var <= hi && e == cudaSuccess; var++) {
-#define CALL(KMV)                                                                                          \
-    e = with_norm ? (pow2 ? dispatch_s2<KMV, true, true>(cx, p, var, handled) : dispatch_s2<KMV, false, true>(cx, p, var, handled)) \
-                  : (pow2 ? dispatch_s2<KMV, true, false>(cx, p, var, handled) : dispatch_s2<KMV, false, false>(cx, p, var, handled))
+#define CALL(KMV)                                                                    \
+    AR_SWITCH(ar, e = with_norm ? (dispatch_s2<KMV, ARV, true>(cx, p, var, handled)) \
+                                : (dispatch_s2<KMV, ARV, false>(cx, p, var, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;
         case KM_NONLINEAR: CALL(KM_NONLINEAR); break;
@@ -278,9 +283,9 @@ cudaError_t kx_prepare()
     bool handled;
     cudaError_t e = cudaSuccess;
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
-        for (int pw = 0; pw < 2 && e == cudaSuccess; pw++)
+        for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
             for (int nm = 0; nm < 2 && e == cudaSuccess; nm++)
-                e = kx_smooth2(cx, km, pw != 0, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, &handled);
+                e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, &handled);
     done = e == cudaSuccess;
     return e;
 }

@@ -49,6 +49,7 @@ __device__ __forceinline__ Ay4 load_ay(const double* __restrict__ cv, i64 b, i64
 }
 
 constexpr int PBX = 32, PBY = 8;
+int g_prolong_occ = 8;  // resident CTAs per SM of prolong_correct_zmarch (kt_prepare)
 
 __global__ void __launch_bounds__(PBX* PBY) prolong_correct_zmarch(ProlongFastP p)
 {
@@ -65,29 +66,52 @@ __global__ void __launch_bounds__(PBX* PBY) prolong_correct_zmarch(ProlongFastP 
     Ay4 a = load_ay(p.coarse, cb, p.gc.pitch);
     i64 c = gs_idx(p.gf, xo, yo, z0);
     const i64 pitch = p.gf.pitch, plane = p.gf.plane;
-    for (int z = z0; z < z1; z++, zg++, c += plane) {
-        Ay4 e = a;
+    const double2 zero2 = make_double2(0.0, 0.0);
+    auto mid = [](const Ay4& a, const Ay4& n) {
+        Ay4 e;
+        e.oo = 0.5 * a.oo + 0.5 * n.oo;
+        e.eo = 0.5 * a.eo + 0.5 * n.eo;
+        e.oe = 0.5 * a.oe + 0.5 * n.oe;
+        e.ee = 0.5 * a.ee + 0.5 * n.ee;
+        return e;
+    };
+    auto put = [&](i64 at, double2 v0, double2 v1, const Ay4& e) {
+        v0.x = v0.x + e.oo;
+        v0.y = v0.y + e.eo;
+        if (has_xe) *reinterpret_cast<double2*>(p.vout + at) = v0;
+        else p.vout[at] = v0.x;
+        if (has_ye) {
+            v1.x = v1.x + e.oe;
+            v1.y = v1.y + e.ee;
+            if (has_xe) *reinterpret_cast<double2*>(p.vout + at + pitch) = v1;
+            else p.vout[at + pitch] = v1.x;
+        }
+    };
+    // Two fine planes per iteration, all four v rows loaded before anything is stored: vin may alias vout (in-place
+    // correction), so the compiler cannot hoist a load over a store by itself, and one 16-byte load in flight per
+    // thread is not enough to cover the HBM latency.  Of two consecutive planes exactly one is odd (needs the next
+    // coarse plane).
+    for (int z = z0; z < z1; z += 2, zg += 2, c += 2 * plane) {
+        const bool two = z + 1 < z1;
+        const double2 v00 = *reinterpret_cast<const double2*>(p.vin + c);
+        const double2 v01 = has_ye ? *reinterpret_cast<const double2*>(p.vin + c + pitch) : zero2;
+        const double2 v10 = two ? *reinterpret_cast<const double2*>(p.vin + c + plane) : zero2;
+        const double2 v11 = (two && has_ye) ? *reinterpret_cast<const double2*>(p.vin + c + plane + pitch) : zero2;
+        Ay4 e0 = a, e1 = a;
         if (zg & 1) {
             cb += p.gc.plane;
             const Ay4 n = load_ay(p.coarse, cb, p.gc.pitch);
-            e.oo = 0.5 * a.oo + 0.5 * n.oo;
-            e.eo = 0.5 * a.eo + 0.5 * n.eo;
-            e.oe = 0.5 * a.oe + 0.5 * n.oe;
-            e.ee = 0.5 * a.ee + 0.5 * n.ee;
+            e0 = mid(a, n);
+            a = n;
+            e1 = n;
+        } else if (two) {
+            cb += p.gc.plane;
+            const Ay4 n = load_ay(p.coarse, cb, p.gc.pitch);
+            e1 = mid(a, n);
             a = n;
         }
-        double2 v0 = *reinterpret_cast<const double2*>(p.vin + c);
-        v0.x = v0.x + e.oo;
-        v0.y = v0.y + e.eo;
-        if (has_xe) *reinterpret_cast<double2*>(p.vout + c) = v0;
-        else p.vout[c] = v0.x;
-        if (has_ye) {
-            double2 v1 = *reinterpret_cast<const double2*>(p.vin + c + pitch);
-            v1.x = v1.x + e.oe;
-            v1.y = v1.y + e.ee;
-            if (has_xe) *reinterpret_cast<double2*>(p.vout + c + pitch) = v1;
-            else p.vout[c + pitch] = v1.x;
-        }
+        put(c, v00, v01, e0);
+        if (two) put(c + plane, v10, v11, e1);
     }
 }
 
@@ -139,7 +163,7 @@ struct RRCfg {
 
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
-template <int KM, bool POW2, int CX, int CY, int NSTAGE>
+template <int KM, int AR, int CX, int CY, int NSTAGE>
 __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 32 + 32, 2)
     resid_restrict_tma(const __grid_constant__ CUtensorMap map_v, ResidRestrictP p)
 {
@@ -239,10 +263,10 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
             }
             const bool mz = zgA + t <= p.gf.nz;
             double den;
-            r11 = canon_residual<KM, POW2>(C1.x, C1.y, W1, C2.x, S.x, U1.x, D1.x, f1.x, a1.x, p.k, den);
-            r21 = canon_residual<KM, POW2>(C1.y, E1, C1.x, C2.y, S.y, U1.y, D1.y, f1.y, a1.y, p.k, den);
-            r12 = canon_residual<KM, POW2>(C2.x, C2.y, W2, N.x, C1.x, U2.x, D2.x, f2.x, a2.x, p.k, den);
-            r22 = canon_residual<KM, POW2>(C2.y, E2, C2.x, N.y, C1.y, U2.y, D2.y, f2.y, a2.y, p.k, den);
+            r11 = canon_residual<KM, AR>(C1.x, C1.y, W1, C2.x, S.x, U1.x, D1.x, f1.x, a1.x, p.k, den);
+            r21 = canon_residual<KM, AR>(C1.y, E1, C1.x, C2.y, S.y, U1.y, D1.y, f1.y, a1.y, p.k, den);
+            r12 = canon_residual<KM, AR>(C2.x, C2.y, W2, N.x, C1.x, U2.x, D2.x, f2.x, a2.x, p.k, den);
+            r22 = canon_residual<KM, AR>(C2.y, E2, C2.x, N.y, C1.y, U2.y, D2.y, f2.y, a2.y, p.k, den);
             r11 = (mz && mx1 && my1) ? r11 : 0.0;
             r21 = (mz && mx2 && my1) ? r21 : 0.0;
             r12 = (mz && mx1 && my2) ? r12 : 0.0;
@@ -331,7 +355,7 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
                 if (KM >= KM_NEWTON_EXP) na = __ldg(p.aux + cn);
             }
             double den;
-            double r = canon_residual<KM, POW2>(C, E, W, N, S, U, D, fv, av, p.k, den);
+            double r = canon_residual<KM, AR>(C, E, W, N, S, U, D, fv, av, p.k, den);
             r = (mxy && zgA + t <= p.gf.nz) ? r : 0.0;
             if (used) slot(t)[so] = r;
             D = C; C = U; fv = nf; av = na;
@@ -359,7 +383,8 @@ cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
     const int npx = (gf.nx + 1) / 2, npy = (gf.ny + 1) / 2;
     ProlongFastP p{gf, gc, zb, ze, 0, vin, vout, coarse};
     const int tiles = ((npx + PBX - 1) / PBX) * ((npy + PBY - 1) / PBY);
-    p.zchunk = gs_pick_zchunk(cx, tiles, ze - zb, 64);
+    if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tiles, ze - zb, g_prolong_occ, 2, 8, 128, true);
+    else p.zchunk = gs_pick_zchunk(cx, tiles, ze - zb, 64);
     p.zchunk += p.zchunk & 1;  // even chunks: every chunk starts on the same plane parity
     dim3 grid((npx + PBX - 1) / PBX, (npy + PBY - 1) / PBY, (ze - zb + p.zchunk - 1) / p.zchunk);
     prolong_correct_zmarch<<<grid, dim3(PBX, PBY), 0, cx.stream>>>(p);
@@ -370,14 +395,17 @@ cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
 
 namespace {
 
-template <int KM, bool POW2, int CX, int CY, int NSTAGE>
+template <int KM, int AR, int CX, int CY, int NSTAGE>
 cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 {
     using Cfg = RRCfg<CX, CY, NSTAGE>;
     static bool prepared = false;
+    static int occ = 1;
     if (!prepared) {
-        cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, POW2, CX, CY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, AR, CX, CY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
+        if (e == cudaSuccess)
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, resid_restrict_tma<KM, AR, CX, CY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
         if (e != cudaSuccess) return e;
         prepared = true;
     }
@@ -385,25 +413,27 @@ cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
     CUtensorMap mv;
     if (!gs_tensor_map(p.v, p.gf, Cfg::VW, Cfg::VH, &mv)) return cudaSuccess;  // not handled
     const int tx = (p.gc.nx + CX - 1) / CX, ty = (p.gc.ny + CY - 1) / CY;
-    p.zchunk = gs_pick_zchunk(cx, tx * ty, p.zce - p.zcb, 32);
+    // a chunk of coarse planes re-reads three fine planes (1.5 coarse-plane times) and fills the ring
+    if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tx * ty, p.zce - p.zcb, occ, 3, 4, 64, false);
+    else p.zchunk = gs_pick_zchunk(cx, tx * ty, p.zce - p.zcb, 32);
     dim3 grid(tx, ty, (p.zce - p.zcb + p.zchunk - 1) / p.zchunk);
-    resid_restrict_tma<KM, POW2, CX, CY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, p);
+    resid_restrict_tma<KM, AR, CX, CY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, p);
     *handled = true;
     return cudaGetLastError();
 }
 
-template <int KM, bool POW2>
+template <int KM, int AR>
 cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, bool* handled)
 {
-    if (cfg == 0) return launch_rr<KM, POW2, 32, 8, 4>(cx, p, handled);
-    return launch_rr<KM, POW2, 32, 4, 4>(cx, p, handled);
+    if (cfg == 0) return launch_rr<KM, AR, 32, 8, 4>(cx, p, handled);
+    return launch_rr<KM, AR, 32, 4, 4>(cx, p, handled);
 }
 
 }  // namespace
 
 // f_{l+1}(coarse interior planes [zcb, zce)) = R(f_l - A_l v_l); the fine level must hold v planes
 // 2*Zc-2 .. 2*Zc+2 of every coarse plane Zc it is asked for
-cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, bool pow2, const Geom& gf, const Geom& gc, int zcb, int zce,
+cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
                               const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled)
 {
     *handled = false;
@@ -416,7 +446,7 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, bool pow2, const Geom
     ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse};
     cudaError_t e = cudaSuccess;
     for (int c = v ? cfg : 0; c <= (v ? cfg : 1) && e == cudaSuccess; c++) {
-#define CALL(KMV) e = pow2 ? dispatch_rr<KMV, true>(cx, p, c, handled) : dispatch_rr<KMV, false>(cx, p, c, handled)
+#define CALL(KMV) AR_SWITCH(ar, e = (dispatch_rr<KMV, ARV>(cx, p, c, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;
         case KM_NONLINEAR: CALL(KM_NONLINEAR); break;
@@ -439,8 +469,9 @@ cudaError_t kt_prepare()
     bool handled;
     cudaError_t e = cudaSuccess;
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
-        for (int pw = 0; pw < 2 && e == cudaSuccess; pw++)
-            e = kt_resid_restrict(cx, km, pw != 0, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+        for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
+            e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_prolong_occ, prolong_correct_zmarch, PBX * PBY, 0);
     done = e == cudaSuccess;
     return e;
 }
