@@ -561,7 +561,7 @@ uint64_t parity_key(const gs_handle* h)
     key |= (uint64_t)h->opt_kernels << 40;
     key |= (uint64_t)(h->cx.tune.smooth_variant & 0x3f) << 32;
     key ^= (uint64_t)(h->cx.tune.zchunk & 0xfff) << 20;
-    key ^= (uint64_t)(h->cx.tune.rr_variant & 1) << 19;
+    key ^= (uint64_t)(h->cx.tune.rr_variant & 3) << 18;
     key ^= (uint64_t)(h->lev[0].pre_valid & 3) << 15;
     key ^= (uint64_t)(h->cx.tune.fuse2 & 7) << 12;
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
@@ -914,14 +914,14 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* ev = getenv("GPUSOLVE_SMOOTH_VARIANT")) h->cx.tune.smooth_variant = atoi(ev);
     if (const char* ev = getenv("GPUSOLVE_ZCHUNK")) h->cx.tune.zchunk = std::max(1, atoi(ev));
     if (const char* ev = getenv("GPUSOLVE_FAST_MIN_N")) h->cx.tune.fast_min_n = atoi(ev);
-    h->cx.tune.rr_variant = 0;
+    h->cx.tune.rr_variant = 2;  // 32x8 coarse columns, five-stage ring
     h->cx.tune.fuse2 = 1;
     h->cx.tune.fuse2_min_n = 96;
     h->cx.tune.zchunk2 = 128;
     h->cx.tune.wave = 1;
     if (const char* ev = getenv("GPUSOLVE_WAVE")) h->cx.tune.wave = atoi(ev) != 0;
-    if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(3, atoi(ev)));
-    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = atoi(ev) != 0;
+    if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(2, atoi(ev)));
+    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = std::max(0, std::min(2, atoi(ev)));
     e = kf_prepare();
     if (e == cudaSuccess) e = kt_prepare();
     if (e == cudaSuccess) e = kx_prepare();
@@ -1412,9 +1412,9 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         for (auto& L : h->lev) L.ar = (L.pow2 ? 1 : 0) | ((L.unit && value != 0) ? 2 : 0);
-    } else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
+    } else if (n == "rr_variant") h->cx.tune.rr_variant = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
     else if (n == "fuse2") {
-        h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(3, value));
+        h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
         h->lev[0].pre_valid = 0;
     } else if (n == "fuse2_min_n") h->cx.tune.fuse2_min_n = (int)value;
     else if (n == "zchunk2") h->cx.tune.zchunk2 = (int)std::max<int64_t>(8, value);

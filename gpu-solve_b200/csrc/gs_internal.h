@@ -63,8 +63,8 @@ struct Tune {
     int smooth_variant;  // 0 simple, 1x z-march through L1, 2x TMA-staged z-march (kernels_fast.cu)
     int zchunk;          // planes per CTA of the z-marching kernels
     int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
-    int rr_variant;      // tile of the fused residual+restriction kernel: 0 = 32x8 coarse columns, 1 = 32x4
-    int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1.. = tile variant + 1
+    int rr_variant;      // fused residual+restriction kernel: 0 = 32x8 coarse columns / 4 stages, 1 = 32x4 / 4, 2 = 32x8 / 5
+    int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1 = five-stage ring, 2 = four-stage
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
     int zchunk2;         // planes per CTA of the two-sweep kernel
     int wave;            // 1: size z chunks so the grid fills whole waves of resident CTAs (gs_pick_zchunk_waves)

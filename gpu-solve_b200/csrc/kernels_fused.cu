@@ -48,8 +48,8 @@ struct S2Cfg {
     static constexpr int STAGE = V_BYTES + F_BYTES;
     static constexpr int S1_BYTES = BW * FH * 8;
     static constexpr int NCONS = BW * FH / 2;  // two first-sweep rows per thread
-    static constexpr int THREADS = NCONS + 32;
-    static constexpr int SMEM = NSTAGE * STAGE + 2 * S1_BYTES + 2 * NSTAGE * 8 + 128;
+    static constexpr int THREADS = NCONS;      // no producer warp: thread 0 issues the TMA loads (512 threads -> 64 registers at 2 CTAs/SM)
+    static constexpr int SMEM = NSTAGE * STAGE + 2 * S1_BYTES + (NSTAGE + 1) * 8 + 128;
     static_assert(TY % 2 == 0, "two rows per thread");
     static_assert(NCONS % 32 == 0 && NCONS <= 992, "consumer threads");
 };
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
     unsigned char* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
     double* s1ring = (double*)(smem + NSTAGE * Cfg::STAGE);
     uint64_t* full = (uint64_t*)(smem + NSTAGE * Cfg::STAGE + 2 * Cfg::S1_BYTES);
-    uint64_t* empty = full + NSTAGE;
+    uint64_t* s1bar = full + NSTAGE;  // phase p completes when every warp has stored its first-sweep plane p+1
 
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * Cfg::TXO + 1, y0 = blockIdx.y * TY + 1;  // first output point of the tile
@@ -74,30 +74,24 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
     // plane index q: local plane z0-2+q.  v planes q = 0 .. nzo+3, f planes q = 1 .. nzo+2,
     // first sweep on q = 1 .. nzo+2, second sweep on q = 2 .. nzo+1
 
+    // plane P of the input -> ring stage P % NSTAGE (thread 0 only).  A stage is free for plane P once every warp has
+    // finished the iteration that read plane P - NSTAGE, which the split-phase barrier s1bar below tells.
+    auto issue = [&](int P) {
+        const int s = P % NSTAGE;
+        const bool has_f = P >= 1 && P <= nzo + 2;
+        mbar_expect_tx(&full[s], Cfg::V_BYTES + (has_f ? Cfg::F_BYTES : 0));
+        unsigned char* st = smem + s * Cfg::STAGE;
+        // out-of-range rows / planes / columns (negative or past the array) are zero-filled by TMA
+        tma_load_3d(st, &map_v, &full[s], GS_XOFF + x0 - 2, y0 - 2, z0 - 2 + P);
+        if (has_f) tma_load_3d(st + Cfg::V_BYTES, &map_f, &full[s], GS_XOFF + x0 - 2, y0 - 1, z0 - 2 + P);
+    };
     if (tid == 0) {
-        for (int s = 0; s < NSTAGE; s++) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], Cfg::NCONS / 32);
-        }
+        for (int s = 0; s < NSTAGE; s++) mbar_init(&full[s], 1);
+        mbar_init(s1bar, Cfg::NCONS / 32);
         mbar_fence_init();
+        for (int P = 0; P < NSTAGE && P <= nzo + 3; P++) issue(P);
     }
     __syncthreads();
-
-    if (tid >= Cfg::NCONS) {
-        if (tid == Cfg::NCONS) {
-            for (int q = 0; q < nzo + 4; q++) {
-                const int s = q % NSTAGE;
-                if (q >= NSTAGE) mbar_wait(&empty[s], ((q / NSTAGE) - 1) & 1);
-                const bool has_f = q >= 1 && q <= nzo + 2;
-                mbar_expect_tx(&full[s], Cfg::V_BYTES + (has_f ? Cfg::F_BYTES : 0));
-                unsigned char* st = smem + s * Cfg::STAGE;
-                // out-of-range rows / planes / columns (negative or past the array) are zero-filled by TMA
-                tma_load_3d(st, &map_v, &full[s], GS_XOFF + x0 - 2, y0 - 2, z0 - 2 + q);
-                if (has_f) tma_load_3d(st + Cfg::V_BYTES, &map_f, &full[s], GS_XOFF + x0 - 2, y0 - 1, z0 - 2 + q);
-            }
-        }
-        return;
-    }
 
     // ---- consumers ----
     const int lx = tid & (BW - 1), tr = tid / BW;
@@ -130,8 +124,6 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
     double sq = 0.0;
     mbar_wait(&full[0], 0);
     double Da = vbox(0)[iv], Db = vbox(0)[iv + BW];
-    __syncwarp();
-    if (lane0) mbar_arrive(&empty[0]);
     mbar_wait(&full[1 % NSTAGE], (1 / NSTAGE) & 1);
     double Ca = vbox(1)[iv], Cb = vbox(1)[iv + BW];
     double D1a = 0.0, D1b = 0.0, C1a = 0.0, C1b = 0.0;  // first-sweep values of the own columns
@@ -153,8 +145,6 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
         const double Ea = vb[iv + eo], Wa = vb[iv - wo], Sa = vb[iv - BW];
         const double Eb = vb[iv + BW + eo], Wb = vb[iv + BW - wo], Nb = vb[iv + 2 * BW];
         const double fa = fbox(q)[is], fb = fbox(q)[is + BW];
-        __syncwarp();
-        if (lane0) mbar_arrive(&empty[q % NSTAGE]);
 
         // ---- first sweep on plane q ----
         double dena, denb;
@@ -168,11 +158,18 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
             if (oa) sq += ra * ra;
             if (ob) sq += rb * rb;
         }
-        double* sw = s1slot(q);
-        sw[is] = U1a;
-        sw[is + BW] = U1b;
-
         // ---- second sweep on plane q-1 (its first-sweep neighbours were stored one iteration ago) ----
+        // Split-phase CTA barrier: a warp ARRIVES after storing its first-sweep plane (end of the iteration) and WAITS
+        // here, after the next plane's first sweep, so stragglers have most of an iteration of slack.  Passing the
+        // wait also means every warp has finished iteration q-1, i.e. its reads of slot (q-2)&1 = q&1, which is
+        // the slot written below.
+        if (q >= 2) {
+            mbar_wait(s1bar, (q - 2) & 1);
+            if (tid == 0) {  // every warp is past iteration q-1: the stages of planes <= q-1 are free
+                if (q == 2 && NSTAGE <= nzo + 3) issue(NSTAGE);
+                if (q - 1 + NSTAGE <= nzo + 3) issue(q - 1 + NSTAGE);
+            }
+        }
         if (q >= 3) {
             const double* sr = s1slot(q - 1);
             const double E1a = sr[is + eo], W1a = sr[is - wo], S1a = sr[isS];
@@ -185,10 +182,14 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
             if (oa) p.vout[ca - plane] = na;
             if (ob) p.vout[ca - plane + ab] = nb;
         }
+        double* sw = s1slot(q);
+        sw[is] = U1a;
+        sw[is + BW] = U1b;
+        __syncwarp();
+        if (lane0) mbar_arrive(s1bar);
         Da = Ca; Ca = Ua; Db = Cb; Cb = Ub;
         D1a = C1a; C1a = U1a; D1b = C1b; C1b = U1b;
         fpa = fa; fpb = fb; xpa = xa; xpb = xb;
-        consumer_sync<Cfg::NCONS>();
     }
     if (NORM) {
         __shared__ double sh[32];
@@ -235,9 +236,8 @@ template <int KM, int AR, bool NORM>
 cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool* handled)
 {
     switch (variant) {
-    case 1: return launch_s2<KM, AR, NORM, 14, 3>(cx, p, handled);
-    case 2: return launch_s2<KM, AR, NORM, 22, 3>(cx, p, handled);
-    default: return launch_s2<KM, AR, NORM, 14, 4>(cx, p, handled);
+    case 1: return launch_s2<KM, AR, NORM, 14, 4>(cx, p, handled);
+    default: return launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
     }
 }
 
@@ -255,7 +255,7 @@ cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int z
     }
     Fused2P p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm};
     p.zchunk = cx.tune.zchunk2 > 0 ? cx.tune.zchunk2 : 128;
-    const int lo = vin ? cx.tune.fuse2 - 1 : 0, hi = vin ? cx.tune.fuse2 - 1 : 2;
+    const int lo = vin ? cx.tune.fuse2 - 1 : 0, hi = vin ? cx.tune.fuse2 - 1 : 1;
     cudaError_t e = cudaSuccess;
     for (int var = lo; var <= hi && e == cudaSuccess; var++) {
 #define CALL(KMV)                                                                    \

@@ -426,6 +426,7 @@ template <int KM, int AR>
 cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, bool* handled)
 {
     if (cfg == 0) return launch_rr<KM, AR, 32, 8, 4>(cx, p, handled);
+    if (cfg == 2) return launch_rr<KM, AR, 32, 8, 5>(cx, p, handled);
     return launch_rr<KM, AR, 32, 4, 4>(cx, p, handled);
 }
 
@@ -445,7 +446,7 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& g
     }
     ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse};
     cudaError_t e = cudaSuccess;
-    for (int c = v ? cfg : 0; c <= (v ? cfg : 1) && e == cudaSuccess; c++) {
+    for (int c = v ? cfg : 0; c <= (v ? cfg : 2) && e == cudaSuccess; c++) {
 #define CALL(KMV) AR_SWITCH(ar, e = (dispatch_rr<KMV, ARV>(cx, p, c, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;
