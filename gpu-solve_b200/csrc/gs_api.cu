@@ -914,7 +914,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* ev = getenv("GPUSOLVE_SMOOTH_VARIANT")) h->cx.tune.smooth_variant = atoi(ev);
     if (const char* ev = getenv("GPUSOLVE_ZCHUNK")) h->cx.tune.zchunk = std::max(1, atoi(ev));
     if (const char* ev = getenv("GPUSOLVE_FAST_MIN_N")) h->cx.tune.fast_min_n = atoi(ev);
-    h->cx.tune.rr_variant = 2;  // 32x8 coarse columns, five-stage ring
+    h->cx.tune.rr_variant = 0;  // 32x8 coarse columns, four-stage ring (variant 2, five stages, fails parity when launched back to back: not used)
     h->cx.tune.fuse2 = 1;
     h->cx.tune.fuse2_min_n = 96;
     h->cx.tune.zchunk2 = 128;

@@ -24,6 +24,8 @@
 // each point counted by the CTA whose output tile holds it.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "gs_device.cuh"
 
 namespace {
@@ -198,6 +200,213 @@ __global__ void __launch_bounds__(S2Cfg<TY, NSTAGE>::THREADS, 2) smooth2_tma(con
     }
 }
 
+// ---------------------------------------------------------------------------------
+// smooth2u_tma: the same algorithm with the plane loop unrolled over a full period of its
+// rotating state, so nothing rotates at run time
+// ---------------------------------------------------------------------------------
+// The z-march of smooth2_tma carries three rotating things: the six-stage TMA ring, the two-slot
+// first-sweep ring and the three-deep register queues of the own columns.  Unrolled by six (their
+// common period) every ring stage, slot, mbarrier and queue register is a compile-time constant of
+// the body copy: shared-memory accesses are [one per-thread base register + immediate], the queues
+// need no register moves, and `q % NSTAGE` disappears.  (The rolled kernel issues ~210 instructions
+// per plane for 52 fp64 operations and is issue-bound at 83 % of the issue slots: ncu,
+// profiles/r01h_*.)  Six stages at two CTAs per SM need the smaller 60 x 12 tile.
+template <int TY>
+struct S2uCfg {
+    static constexpr int NSTAGE = 6;
+    static constexpr int BW = 64, TXO = 60;
+    static constexpr int VH = TY + 4, FH = TY + 2;
+    static constexpr int V_BYTES = BW * VH * 8, F_BYTES = BW * FH * 8;
+    static constexpr int STAGE = V_BYTES + F_BYTES;
+    static constexpr int S1_BYTES = BW * FH * 8;
+    static constexpr int NCONS = BW * FH / 2;
+    static constexpr int THREADS = NCONS;
+    static constexpr int RING = NSTAGE * STAGE;
+    static constexpr int BAR_OFF = RING + 2 * S1_BYTES + 1024;  // 1 KB pad: masked edge lanes read one row past a slot
+    static constexpr int SMEM = BAR_OFF + (NSTAGE + 1) * 8 + 128;
+    static_assert(TY % 2 == 0 && NCONS % 32 == 0, "two rows per thread, whole warps");
+};
+
+template <int KM, int AR, bool NORM, int TY>
+__global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __grid_constant__ CUtensorMap map_v,
+                                                                      const __grid_constant__ CUtensorMap map_f, Fused2P p)
+{
+    using Cfg = S2uCfg<TY>;
+    constexpr int BW = Cfg::BW, NS = Cfg::NSTAGE;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+    const uint32_t sbase = smem_u32(smem);
+    const uint32_t bars = sbase + Cfg::BAR_OFF;  // full[0..NS), then s1bar
+    const uint32_t s1bar = bars + NS * 8;
+
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * Cfg::TXO + 1, y0 = blockIdx.y * TY + 1;
+    const int z0 = p.zb + blockIdx.z * p.zchunk;
+    const int z1 = min(z0 + p.zchunk, p.ze);
+    const int nzo = z1 - z0;
+    const int last = nzo + 2;  // first sweep on planes q = 1 .. last, second sweep on 2 .. last-1 (see smooth2_tma)
+
+    // thread 0: plane P of the input -> stage S of the ring
+    auto issue = [&](int P, int S) {
+        const bool has_f = P >= 1 && P <= last;
+        const uint32_t bar = bars + S * 8, dst = sbase + S * Cfg::STAGE;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(Cfg::V_BYTES + (has_f ? Cfg::F_BYTES : 0))
+                     : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+                     "l"(&map_v), "r"(bar), "r"(GS_XOFF + x0 - 2), "r"(y0 - 2), "r"(z0 - 2 + P)
+                     : "memory");
+        if (has_f)
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+                             dst + Cfg::V_BYTES),
+                         "l"(&map_f), "r"(bar), "r"(GS_XOFF + x0 - 2), "r"(y0 - 1), "r"(z0 - 2 + P)
+                         : "memory");
+    };
+    if (tid == 0) {
+        for (int s = 0; s <= NS; s++) {
+            const uint32_t cnt = s < NS ? 1 : Cfg::NCONS / 32;
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bars + s * 8), "r"(cnt));
+        }
+        mbar_fence_init();
+#pragma unroll
+        for (int P = 0; P < NS; P++)
+            if (P <= nzo + 3) issue(P, P);
+    }
+    __syncthreads();
+
+    const int lx = tid & (BW - 1), tr = tid / BW;
+    constexpr int LAST_TR = Cfg::FH / 2 - 1;
+    const int x = x0 - 2 + lx;
+    const int ya = y0 - 1 + 2 * tr, yb = ya + 1;
+    const bool x1ok = lx >= 1 && lx <= BW - 2 && x >= 1 && x <= p.g.nx;
+    const bool a1 = x1ok && ya >= 1 && ya <= p.g.ny;   // first sweep defined (else the zero of the Dirichlet halo)
+    const bool b1 = x1ok && yb <= p.g.ny;
+    const bool xo = lx >= 2 && lx <= BW - 3 && x <= p.g.nx;
+    const bool oa = xo && tr > 0 && ya <= p.g.ny;      // points of the output tile
+    const bool ob = xo && tr < LAST_TR && yb <= p.g.ny;
+    const bool lane0 = (tid & 31) == 0;
+    // per-thread shared-memory base: element (x, ya) of a v box in stage 0; everything else is an immediate away.
+    // Edge lanes (lx = 0, 63; tr = 0, LAST_TR) read neighbours that belong to another row, slot or the pad: those
+    // values only enter results that are masked (a1/b1) or never stored (oa/ob).
+    const uint32_t tb = sbase + ((2 * tr + 1) * BW + lx) * 8;
+    constexpr int ROW = BW * 8;
+    constexpr int FOFF = Cfg::V_BYTES - ROW;                  // (x, ya) of the f box of the same stage
+    constexpr int S1OFF = Cfg::RING - ROW;                    // (x, ya) of first-sweep slot 0
+    const i64 plane = p.g.plane;
+    const i64 ca0 = gs_idx(p.g, min(max(x, 1), p.g.nx), min(max(ya, 1), p.g.ny), z0 - 2);  // plane q = 0
+    const i64 ab = (yb <= p.g.ny && ya >= 1) ? p.g.pitch : 0;
+    double* vo = p.vout + ca0;          // advanced one plane per iteration: (x, ya) on plane q - 1 when the second sweep stores
+    const double* xp = KM >= KM_NEWTON_EXP ? p.aux + ca0 + plane : nullptr;  // (x, ya) on plane q
+    const int qlo = 1 - (p.g.z0 + z0 - 2), qhi = p.g.nz - (p.g.z0 + z0 - 2);  // planes q inside the interior: qlo <= q <= qhi
+
+    double vq[3][2], s1q[3][2], fq[2][2], xq[2][2];
+#pragma unroll
+    for (int i = 0; i < 3; i++) s1q[i][0] = s1q[i][1] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 2; i++) fq[i][0] = fq[i][1] = xq[i][0] = xq[i][1] = 0.0;
+    double sq = 0.0;
+    mbar_wait_a(bars + 0, 0);
+    vq[0][0] = lds_f64(tb);
+    vq[0][1] = lds_f64(tb + ROW);
+    mbar_wait_a(bars + 8, 0);
+    vq[1][0] = lds_f64(tb + Cfg::STAGE);
+    vq[1][1] = lds_f64(tb + Cfg::STAGE + ROW);
+    vq[2][0] = vq[2][1] = 0.0;
+
+    // one plane: K = q mod 6 (ring stage, queue slots, parities), PH = 1 / 2 for the start-up planes q = 1 / 2, else 0
+    auto step = [&](auto Kc, auto PHc, const int q, const uint32_t par) {
+        constexpr int K = decltype(Kc)::value, PH = decltype(PHc)::value;
+        constexpr int SC = K % NS, SU = (K + 1) % NS;                  // stages of planes q, q+1
+        constexpr int iC = K % 3, iU = (K + 1) % 3, iD = (K + 2) % 3;   // queue slots of planes q, q+1, q-1 (q-2 for the first-sweep queue)
+        constexpr int jC = K & 1, jP = (K + 1) & 1;                    // f / first-sweep slot of plane q, of plane q-1
+        const bool zok = q >= qlo && q <= qhi;
+        double xa = 0.0, xb = 0.0;
+        if (KM >= KM_NEWTON_EXP) {
+            if (a1 && zok) xa = xp[0];
+            if (b1 && zok) xb = xp[ab];
+        }
+        mbar_wait_a(bars + SU * 8, SU == 0 ? par ^ 1u : par);
+        const uint32_t c = tb + SC * Cfg::STAGE, u = tb + SU * Cfg::STAGE;
+        vq[iU][0] = lds_f64(u);
+        vq[iU][1] = lds_f64(u + ROW);
+        const double Ea = lds_f64(c + 8), Wa = lds_f64(c - 8), Sa = lds_f64(c - ROW);
+        const double Eb = lds_f64(c + ROW + 8), Wb = lds_f64(c + ROW - 8), Nb = lds_f64(c + 2 * ROW);
+        fq[jC][0] = lds_f64(c + FOFF);
+        fq[jC][1] = lds_f64(c + FOFF + ROW);
+        xq[jC][0] = xa;
+        xq[jC][1] = xb;
+
+        // ---- first sweep on plane q ----
+        double dena, denb;
+        const double ra = canon_residual<KM, AR>(vq[iC][0], Ea, Wa, vq[iC][1], Sa, vq[iU][0], vq[iD][0], fq[jC][0], xa, p.k, dena);
+        const double rb = canon_residual<KM, AR>(vq[iC][1], Eb, Wb, Nb, vq[iC][0], vq[iU][1], vq[iD][1], fq[jC][1], xb, p.k, denb);
+        const double u1a = jacobi_update<KM>(vq[iC][0], ra, dena, p.k);
+        const double u1b = jacobi_update<KM>(vq[iC][1], rb, denb, p.k);
+        // (s1q[iC] held plane q-3, last used by the second sweep of the previous step)
+        const double D1a = s1q[iU][0], D1b = s1q[iU][1];  // plane q-2
+        s1q[iC][0] = (a1 && zok) ? u1a : 0.0;
+        s1q[iC][1] = (b1 && zok) ? u1b : 0.0;
+        if (NORM && PH != 1) {
+            if (q != last) {
+                if (oa) sq += ra * ra;
+                if (ob) sq += rb * rb;
+            }
+        }
+        if (PH != 1) {
+            // split-phase CTA barrier (see smooth2_tma): every warp has finished step q-1
+            mbar_wait_a(s1bar, (uint32_t)jC);
+            if (tid == 0) {
+                if (PH == 2 && NS <= nzo + 3) issue(NS, 0);
+                if (q + NS - 1 <= nzo + 3) issue(q + NS - 1, (K + NS - 1) % NS);
+            }
+        }
+        if (PH == 0) {
+            // ---- second sweep on plane q-1 ----
+            const uint32_t s = tb + S1OFF + jP * Cfg::S1_BYTES;
+            const double E1a = lds_f64(s + 8), W1a = lds_f64(s - 8), S1a = lds_f64(s - ROW);
+            const double E1b = lds_f64(s + ROW + 8), W1b = lds_f64(s + ROW - 8), N1b = lds_f64(s + 2 * ROW);
+            double d2;
+            const double r2a = canon_residual<KM, AR>(s1q[iD][0], E1a, W1a, s1q[iD][1], S1a, s1q[iC][0], D1a, fq[jP][0], xq[jP][0], p.k, d2);
+            const double na = jacobi_update<KM>(s1q[iD][0], r2a, d2, p.k);
+            const double r2b = canon_residual<KM, AR>(s1q[iD][1], E1b, W1b, N1b, s1q[iD][0], s1q[iC][1], D1b, fq[jP][1], xq[jP][1], p.k, d2);
+            const double nb = jacobi_update<KM>(s1q[iD][1], r2b, d2, p.k);
+            if (oa) vo[0] = na;
+            if (ob) vo[ab] = nb;
+        }
+        sts_f64(tb + S1OFF + jC * Cfg::S1_BYTES, s1q[iC][0]);
+        sts_f64(tb + S1OFF + jC * Cfg::S1_BYTES + ROW, s1q[iC][1]);
+        __syncwarp();
+        if (lane0) mbar_arrive_a(s1bar);
+        vo += plane;
+        if (KM >= KM_NEWTON_EXP) xp += plane;
+    };
+#define GS_IC(v) std::integral_constant<int, v>()
+    step(GS_IC(1), GS_IC(1), 1, 0u);
+    step(GS_IC(2), GS_IC(2), 2, 0u);
+    int q = 3;
+    uint32_t par = 0;
+    bool more = true;
+#define GS_STEP(K)                       \
+    if (q > last) {                      \
+        more = false;                    \
+        break;                           \
+    }                                    \
+    step(GS_IC(K), GS_IC(0), q, par);    \
+    q++;
+    do {
+        GS_STEP(3) GS_STEP(4) GS_STEP(5)
+    } while (0);
+    while (more) {
+        par ^= 1u;
+        GS_STEP(0) GS_STEP(1) GS_STEP(2) GS_STEP(3) GS_STEP(4) GS_STEP(5)
+    }
+#undef GS_STEP
+#undef GS_IC
+    if (NORM) {
+        __shared__ double sh[32];
+        const double tot = block_sum<Cfg::NCONS>(sq, sh, tid);
+        grid_sum_finish<Cfg::NCONS>(tot, p.nb, sh, tid);
+    }
+}
 template <int KM, int AR, bool NORM, int TY, int NSTAGE>
 cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
 {
@@ -232,13 +441,44 @@ cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
     return cudaGetLastError();
 }
 
+template <int KM, int AR, bool NORM, int TY>
+cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
+{
+    using Cfg = S2uCfg<TY>;
+    static bool prepared = false;
+    static int occ = 1;
+    if (!prepared) {
+        cudaError_t e = cudaFuncSetAttribute(smooth2u_tma<KM, AR, NORM, TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smooth2u_tma<KM, AR, NORM, TY>, Cfg::THREADS, Cfg::SMEM);
+        if (e != cudaSuccess) return e;
+        prepared = true;
+    }
+    if (!p.vin) return cudaSuccess;  // preparation call
+    CUtensorMap mv, mf;
+    if (!gs_tensor_map(p.vin, p.g, Cfg::BW, Cfg::VH, &mv) || !gs_tensor_map(p.f, p.g, Cfg::BW, Cfg::FH, &mf)) return cudaSuccess;
+    const int tx = (p.g.nx + Cfg::TXO - 1) / Cfg::TXO, ty = (p.g.ny + TY - 1) / TY;
+    const int planes = p.ze - p.zb;
+    // every chunk re-reads four planes, recomputes two first-sweep planes and fills the ring
+    if (cx.tune.wave) {
+        p.zchunk = gs_pick_zchunk_waves(cx, tx * ty, planes, occ, 6, min(planes, 16), p.zchunk, false);
+    } else {
+        const int want = (cx.sm_count * 4 + tx * ty - 1) / (tx * ty);
+        p.zchunk = min(p.zchunk, max((planes + want - 1) / want, min(planes, 32)));
+    }
+    dim3 grid(tx, ty, (planes + p.zchunk - 1) / p.zchunk);
+    if (NORM && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;
+    smooth2u_tma<KM, AR, NORM, TY><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    *handled = true;
+    return cudaGetLastError();
+}
+
 template <int KM, int AR, bool NORM>
 cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool* handled)
 {
-    switch (variant) {
-    case 1: return launch_s2<KM, AR, NORM, 14, 4>(cx, p, handled);
-    default: return launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
-    }
+    // the unrolled kernel spills heavily with exp() of the Newton iterate in the loop (KM_NEWTON_EXP, only reached
+    // with the precomputed-coefficient path switched off): that mode keeps the rolled kernel
+    if (variant == 1 || KM == KM_NEWTON_EXP) return launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
+    return launch_s2u<KM, AR, NORM, 12>(cx, p, handled);
 }
 
 }  // namespace
