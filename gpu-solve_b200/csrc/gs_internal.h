@@ -130,4 +130,5 @@ cudaError_t kt_prepare();
 cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
                                double* vout, const double* coarse, bool* handled);
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
-                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled);
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, double* vzero,
+                              bool* handled);  // vzero (optional): coarse array whose interior points are set to zero in the same pass

@@ -141,6 +141,7 @@ struct ResidRestrictP {
     const double* f;
     const double* aux;
     double* coarse;
+    double* vzero;  // optional: coarse v, interior zeroed here (CpuSolver.cpp:100-101 v.fill(0)) instead of by a memset
 };
 
 template <int CX, int CY, int NSTAGE>
@@ -311,7 +312,10 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
             TERM(0.5, 1.0, sA[oO + Cfg::ROW_O + 1], sB[oO + Cfg::ROW_O + 1], sC[oO + Cfg::ROW_O + 1])
             TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O + 1], sB[oO + 2 * Cfg::ROW_O + 1], sC[oO + 2 * Cfg::ROW_O + 1])
 #undef TERM
-            if (live) p.coarse[cc] = acc;
+            if (live) {
+                p.coarse[cc] = acc;
+                if (p.vzero) p.vzero[cc] = 0.0;
+            }
             cc += p.gc.plane;
         }
     } else {
@@ -435,7 +439,8 @@ cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, b
 // f_{l+1}(coarse interior planes [zcb, zce)) = R(f_l - A_l v_l); the fine level must hold v planes
 // 2*Zc-2 .. 2*Zc+2 of every coarse plane Zc it is asked for
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
-                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled)
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, double* vzero,
+                              bool* handled)
 {
     *handled = false;
     int cfg = 0;
@@ -444,7 +449,7 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& g
         if (gc.nx < 24 || gc.ny < 8 || zce - zcb < 4) return cudaSuccess;  // small levels: unfused simple kernels
         cfg = cx.tune.rr_variant;
     }
-    ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse};
+    ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse, vzero};
     cudaError_t e = cudaSuccess;
     for (int c = v ? cfg : 0; c <= (v ? cfg : 2) && e == cudaSuccess; c++) {
 #define CALL(KMV) AR_SWITCH(ar, e = (dispatch_rr<KMV, ARV>(cx, p, c, handled)))
@@ -471,7 +476,7 @@ cudaError_t kt_prepare()
     cudaError_t e = cudaSuccess;
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
         for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
-            e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+            e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nullptr, &handled);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_prolong_occ, prolong_correct_zmarch, PBX * PBY, 0);
     done = e == cudaSuccess;
     return e;
