@@ -63,8 +63,6 @@ struct Level {
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
     bool coef_valid;
     int gv;           // slabs: ghost planes of v that are current on each side (0..2); refreshed lazily by need_v_halo
-    bool v_halo_clean;  // nothing but the V-cycle operators ever wrote v / vtmp (no gs_set_field): halo and padding are still zero
-    bool v_zeroed;      // the fused residual+restriction just zeroed the interior of v (enqueue_vcycle skips the memset)
     int pre_valid;    // vtmp == this many Jacobi sweeps of v for the current f/aux (written by the fused sweep+norm kernels)
 };
 
@@ -85,7 +83,7 @@ struct gs_handle {
     LaunchCtx cx;
     double* h_norm;  // pinned
     uint64_t launches;
-    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi, opt_fuse_zero;
+    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
     std::map<uint64_t, int> graphs_pre_valid;      // lev[0].pre_valid after a replay of each graph
@@ -458,7 +456,7 @@ int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, dou
 }
 
 // compResidual(level) ; restrict(r -> f_{level+1})     src/cpu/CpuSolver.cpp:93-98
-int do_restrict_residual(gs_handle* h, int level, bool zero_coarse_v = false)
+int do_restrict_residual(gs_handle* h, int level)
 {
     Level& L = h->lev[level];
     Level& C = h->lev[level + 1];
@@ -476,17 +474,8 @@ int do_restrict_residual(gs_handle* h, int level, bool zero_coarse_v = false)
         int czb, cze;
         coarse_range(h, level, &czb, &cze);
         bool handled = false;
-        // modes 0 and 2 start the coarse solve from v = 0 (src/cpu/CpuSolver.cpp:100-101): on one GPU the kernel zeroes the
-        // interior of coarse v alongside its f store; halo and padding of v are never written by the V-cycle
-        double* vzero = (h->world == 1 && zero_coarse_v && C.v_halo_clean && h->opt_fuse_zero) ? C.v : nullptr;
-        CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, vzero, &handled));
-        if (handled) {
-            if (vzero) {
-                C.v_zeroed = true;
-                C.pre_valid = 0;
-            }
-            return finish_coarse(h, level, C.f);
-        }
+        CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
+        if (handled) return finish_coarse(h, level, C.f);
     }
     CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
     GS(do_restrict(h, level, L.r, C.f, nullptr));
@@ -544,11 +533,9 @@ int enqueue_vcycle(gs_handle* h)
     const int last = (int)h->lev.size() - 1;
     for (int i = 0; i < last; i++) {
         GS(do_smooth(h, i, h->p.pre));
-        h->lev[i + 1].v_zeroed = false;
-        GS(do_restrict_residual(h, i, h->p.mode != GS_MODE_NONLINEAR));
-        if (h->p.mode != GS_MODE_NONLINEAR) {
-            if (!h->lev[i + 1].v_zeroed) GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));
-        } else GS(do_fas_coarse_rhs(h, i));
+        GS(do_restrict_residual(h, i));
+        if (h->p.mode != GS_MODE_NONLINEAR) GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));
+        else GS(do_fas_coarse_rhs(h, i));
     }
     GS(do_smooth(h, last, h->p.pre + h->p.post));
     if ((h->p.pre + h->p.post) & 1) {  // restore buffer parity on the (tiny) coarsest level
@@ -580,8 +567,6 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
     key ^= (uint64_t)(h->lev[0].ar & 3) << 10;
     key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
-    key ^= (uint64_t)(h->opt_fuse_zero & 1) << 8;
-    for (size_t l = 0; l < h->lev.size(); l++) key ^= (uint64_t)(h->lev[l].v_halo_clean ? 0 : 1) << (24 + (l & 7));
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     // slabs: which ghost planes are current decides which exchanges the captured cycle contains
@@ -821,7 +806,6 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_graph = 1;
     h->opt_timing = 0;
     h->opt_fuse_norm = 1;
-    h->opt_fuse_zero = 1;
     h->opt_graph_multi = 1;  // capture the NCCL halo exchanges of a slab V-cycle into the graph as well
     h->comm = nullptr;
     h->h_norm = nullptr;
@@ -884,7 +868,6 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
         PointK& k = L.k;
         for (int i = 0; i < 7; i++) k.c[i] = p->stencil_val[i];
         k.hh = L.h * L.h;
-        L.v_halo_clean = true;
         L.pow2 = is_pow2(k.hh);
         k.inv_hh = L.pow2 ? 1.0 / k.hh : 0.0;
         bool unit = true;
@@ -931,14 +914,14 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* ev = getenv("GPUSOLVE_SMOOTH_VARIANT")) h->cx.tune.smooth_variant = atoi(ev);
     if (const char* ev = getenv("GPUSOLVE_ZCHUNK")) h->cx.tune.zchunk = std::max(1, atoi(ev));
     if (const char* ev = getenv("GPUSOLVE_FAST_MIN_N")) h->cx.tune.fast_min_n = atoi(ev);
-    h->cx.tune.rr_variant = 0;  // 32x8 coarse columns, four-stage ring (variant 2, five stages, fails parity when launched back to back: not used)
+    h->cx.tune.rr_variant = 1;  // six-stage ring
     h->cx.tune.fuse2 = 1;
     h->cx.tune.fuse2_min_n = 96;
     h->cx.tune.zchunk2 = 128;
     h->cx.tune.wave = 1;
     if (const char* ev = getenv("GPUSOLVE_WAVE")) h->cx.tune.wave = atoi(ev) != 0;
     if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(2, atoi(ev)));
-    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = std::max(0, std::min(2, atoi(ev)));
+    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = atoi(ev) != 0;
     e = kf_prepare();
     if (e == cudaSuccess) e = kt_prepare();
     if (e == cudaSuccess) e = kx_prepare();
@@ -1167,7 +1150,6 @@ static int field_io(gs_handle* h, int level, int field, double* host, int layout
         CU(cudaStreamSynchronize(h->stream));
         L.pre_valid = 0;
         if (field == GS_FIELD_V) L.gv = 2;  // every rank received its ghost planes from the dense array
-        if (field == GS_FIELD_V) L.v_halo_clean = false;  // the caller may have written the halo: zero it with a memset from now on
         if (field == GS_FIELD_NEWTONV) L.coef_valid = false;
         if (field == GS_FIELD_NEWTONF) h->newton_begun = true;
     }
@@ -1423,7 +1405,6 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->opt_fuse_norm = value != 0;
         h->lev[0].pre_valid = false;
     }
-    else if (n == "fuse_zero") h->opt_fuse_zero = value != 0;
     else if (n == "timing") h->opt_timing = value != 0;
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
@@ -1431,7 +1412,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         for (auto& L : h->lev) L.ar = (L.pow2 ? 1 : 0) | ((L.unit && value != 0) ? 2 : 0);
-    } else if (n == "rr_variant") h->cx.tune.rr_variant = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
+    } else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
     else if (n == "fuse2") {
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
         h->lev[0].pre_valid = 0;

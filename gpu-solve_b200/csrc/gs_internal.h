@@ -63,7 +63,7 @@ struct Tune {
     int smooth_variant;  // 0 simple, 1x z-march through L1, 2x TMA-staged z-march (kernels_fast.cu)
     int zchunk;          // planes per CTA of the z-marching kernels
     int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
-    int rr_variant;      // fused residual+restriction kernel: 0 = 32x8 coarse columns / 4 stages, 1 = 32x4 / 4, 2 = 32x8 / 5
+    int rr_variant;      // fused residual+restriction kernel: 0 = five-stage ring, 1 = six-stage
     int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1 = five-stage ring, 2 = four-stage
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
     int zchunk2;         // planes per CTA of the two-sweep kernel
@@ -130,5 +130,4 @@ cudaError_t kt_prepare();
 cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
                                double* vout, const double* coarse, bool* handled);
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
-                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, double* vzero,
-                              bool* handled);  // vzero (optional): coarse array whose interior points are set to zero in the same pass
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled);

@@ -141,11 +141,16 @@ struct ResidRestrictP {
     const double* f;
     const double* aux;
     double* coarse;
-    double* vzero;  // optional: coarse v, interior zeroed here (CpuSolver.cpp:100-101 v.fill(0)) instead of by a memset
 };
 
+// There is no producer warp: thread 0 issues the TMA loads right after the per-coarse-plane CTA barrier, which already
+// tells that every warp is done with the planes before it (no empty barriers).  An earlier version with a producer warp
+// and full/empty mbarriers lost parity when launched back to back (a stage was refilled while slow warps still read it;
+// tools/debug_ops.py reproduces such races), and was slower.
 template <int CX, int CY, int NSTAGE>
 struct RRCfg {
+    // the first coarse plane reads v planes 0..4 before the first CTA barrier, so the ring must hold five
+    static_assert(NSTAGE >= 5, "resid_restrict_tma needs at least five stages");
     static constexpr int FX = 2 * CX, FY = 2 * CY;
     static constexpr int VW = FX + 4, VH = FY + 3;  // v box: x from 2*X0-3 (16-byte aligned start), y from 2*Y0-2
     static constexpr int V_BYTES = VW * VH * 8;
@@ -158,14 +163,14 @@ struct RRCfg {
     static constexpr int NSTRIP_USED = RH + FX;
     static constexpr int NSTRIP = (NSTRIP_USED + 31) / 32 * 32;
     static constexpr int NCONS = NCOMP + NSTRIP;
-    static constexpr int THREADS = NCONS + 32;
-    static constexpr int SMEM = NSTAGE * V_STRIDE + NSLOT * RSLOT * 8 + 2 * NSTAGE * 8 + 128;
+    static constexpr int THREADS = NCONS;
+    static constexpr int SMEM = NSTAGE * V_STRIDE + NSLOT * RSLOT * 8 + NSTAGE * 8 + 128;
 };
 
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
 template <int KM, int AR, int CX, int CY, int NSTAGE>
-__global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 32 + 32, 2)
+__global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
     resid_restrict_tma(const __grid_constant__ CUtensorMap map_v, ResidRestrictP p)
 {
     using Cfg = RRCfg<CX, CY, NSTAGE>;
@@ -173,7 +178,6 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
     unsigned char* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
     double* rbuf = (double*)(smem + NSTAGE * Cfg::V_STRIDE);
     uint64_t* full = (uint64_t*)(rbuf + Cfg::NSLOT * Cfg::RSLOT);
-    uint64_t* empty = full + NSTAGE;
 
     const int tid = threadIdx.x;
     const int X0 = 1 + blockIdx.x * CX, Y0 = 1 + blockIdx.y * CY;
@@ -185,30 +189,27 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
     const int zfA = zgA - p.gf.z0;            // the same, local
     const int nvp = 2 * nzc + 3;              // v planes zfA-1 .. zfA+2*nzc+1
 
+    auto issue = [&](int q) {  // v plane q of this CTA -> ring stage q % NSTAGE
+        const int s = q % NSTAGE;
+        mbar_expect_tx(&full[s], Cfg::V_BYTES);
+        tma_load_3d(smem + s * Cfg::V_STRIDE, &map_v, &full[s], GS_XOFF + xf0 - 3, yf0 - 2, zfA - 1 + q);
+    };
+    int next = 0;  // thread 0: first plane not yet requested
     if (tid == 0) {
-        for (int s = 0; s < NSTAGE; s++) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], Cfg::NCONS / 32);
-        }
+        for (int s = 0; s < NSTAGE; s++) mbar_init(&full[s], 1);
         mbar_fence_init();
+        for (; next < NSTAGE && next < nvp; next++) issue(next);
     }
     __syncthreads();
-
-    if (tid >= Cfg::NCONS) {
-        if (tid == Cfg::NCONS) {
-            for (int q = 0; q < nvp; q++) {
-                const int s = q % NSTAGE;
-                if (q >= NSTAGE) mbar_wait(&empty[s], ((q / NSTAGE) - 1) & 1);
-                mbar_expect_tx(&full[s], Cfg::V_BYTES);
-                tma_load_3d(smem + s * Cfg::V_STRIDE, &map_v, &full[s], GS_XOFF + xf0 - 3, yf0 - 2, zfA - 1 + q);
-            }
-        }
-        return;
-    }
+    // called right after the CTA barrier that ends coarse plane j — all warps have finished do_plane(2j+2), whose
+    // neighbour reads were the last use of v plane 2j+3: the stages of planes <= 2j+3 are free
+    auto refill = [&](int j) {
+        if (tid == 0)
+            for (; next < nvp && next <= 2 * j + 3 + NSTAGE; next++) issue(next);
+    };
 
     auto vbox = [&](int q) { return (const double*)(smem + (q % NSTAGE) * Cfg::V_STRIDE); };
     auto slot = [&](int t) { return rbuf + (t % Cfg::NSLOT) * Cfg::RSLOT; };
-    const int lane0 = (tid & 31) == 0;
     const i64 pitch = p.gf.pitch, plane = p.gf.plane;
     constexpr int VW = Cfg::VW;
     constexpr int EOFF = Cfg::RH * Cfg::ROW_O;  // even-x block of a residual slot
@@ -226,8 +227,6 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
 
         mbar_wait(&full[0], 0);
         double2 D1 = lds2(vbox(0) + o11), D2 = lds2(vbox(0) + o11 + VW);
-        __syncwarp();
-        if (lane0) mbar_arrive(&empty[0]);
         mbar_wait(&full[1 % NSTAGE], (1 / NSTAGE) & 1);
         double2 C1 = lds2(vbox(1) + o11), C2 = lds2(vbox(1) + o11 + VW);
         // f / aux of the first residual plane
@@ -243,15 +242,8 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
         // one residual plane t (v centre plane q = t+1): own four points, stored to slot t
         auto do_plane = [&](int t) {
             const int q = t + 1;
-            mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
-            const double* vb = vbox(q);
-            const double* vu = vbox(q + 1);
-            const double2 U1 = lds2(vu + o11), U2 = lds2(vu + o11 + VW);
-            const double2 S = lds2(vb + o11 - VW), N = lds2(vb + o11 + 2 * VW);
-            const double W1 = vb[o11 - 1], W2 = vb[o11 + VW - 1], E1 = vb[o11 + 2], E2 = vb[o11 + VW + 2];
-            __syncwarp();
-            if (lane0) mbar_arrive(&empty[q % NSTAGE]);
-            // prefetch f / aux of the next plane (there is one while t < 2*nzc)
+            // prefetch f / aux of the next plane (there is one while t < 2*nzc): requested before the wait for the v
+            // plane, so the wait is part of its lead time
             double2 nf1 = zero2, nf2 = zero2, na1 = zero2, na2 = zero2;
             if (t < 2 * nzc) {
                 const i64 cn = c0 + (i64)(t + 1) * plane;
@@ -262,6 +254,12 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
                     if (ld2) na2 = __ldg(reinterpret_cast<const double2*>(p.aux + cn + pitch));
                 }
             }
+            mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
+            const double* vb = vbox(q);
+            const double* vu = vbox(q + 1);
+            const double2 U1 = lds2(vu + o11), U2 = lds2(vu + o11 + VW);
+            const double2 S = lds2(vb + o11 - VW), N = lds2(vb + o11 + 2 * VW);
+            const double W1 = vb[o11 - 1], W2 = vb[o11 + VW - 1], E1 = vb[o11 + 2], E2 = vb[o11 + VW + 2];
             const bool mz = zgA + t <= p.gf.nz;
             double den;
             r11 = canon_residual<KM, AR>(C1.x, C1.y, W1, C2.x, S.x, U1.x, D1.x, f1.x, a1.x, p.k, den);
@@ -289,6 +287,7 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
             rB11 = r11; rB21 = r21; rB12 = r12; rB22 = r22;
             do_plane(2 * j + 2);
             consumer_sync<Cfg::NCONS>();
+            refill(j);
             const double* sA = slot(2 * j);
             const double* sB = slot(2 * j + 1);
             const double* sC = slot(2 * j + 2);
@@ -312,10 +311,7 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
             TERM(0.5, 1.0, sA[oO + Cfg::ROW_O + 1], sB[oO + Cfg::ROW_O + 1], sC[oO + Cfg::ROW_O + 1])
             TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O + 1], sB[oO + 2 * Cfg::ROW_O + 1], sC[oO + 2 * Cfg::ROW_O + 1])
 #undef TERM
-            if (live) {
-                p.coarse[cc] = acc;
-                if (p.vzero) p.vzero[cc] = 0.0;
-            }
+            if (live) p.coarse[cc] = acc;
             cc += p.gc.plane;
         }
     } else {
@@ -338,26 +334,22 @@ __global__ void __launch_bounds__(CX* CY + ((2 * CY + 1 + 2 * CX + 31) / 32) * 3
 
         mbar_wait(&full[0], 0);
         double D = vbox(0)[o];
-        __syncwarp();
-        if (lane0) mbar_arrive(&empty[0]);
         mbar_wait(&full[1 % NSTAGE], (1 / NSTAGE) & 1);
         double C = vbox(1)[o];
         double fv = mxy ? __ldg(p.f + c0) : 0.0;
         double av = (KM >= KM_NEWTON_EXP && mxy) ? __ldg(p.aux + c0) : 0.0;
         auto do_plane = [&](int t) {
             const int q = t + 1;
-            mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
-            const double* vb = vbox(q);
-            const double U = vbox(q + 1)[o];
-            const double E = vb[o + 1], W = vb[o - 1], N = vb[o + VW], S = vb[o - VW];
-            __syncwarp();
-            if (lane0) mbar_arrive(&empty[q % NSTAGE]);
             double nf = 0.0, na = 0.0;
             if (t < 2 * nzc && mxy) {
                 const i64 cn = c0 + (i64)(t + 1) * plane;
                 nf = __ldg(p.f + cn);
                 if (KM >= KM_NEWTON_EXP) na = __ldg(p.aux + cn);
             }
+            mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
+            const double* vb = vbox(q);
+            const double U = vbox(q + 1)[o];
+            const double E = vb[o + 1], W = vb[o - 1], N = vb[o + VW], S = vb[o - VW];
             double den;
             double r = canon_residual<KM, AR>(C, E, W, N, S, U, D, fv, av, p.k, den);
             r = (mxy && zgA + t <= p.gf.nz) ? r : 0.0;
@@ -429,9 +421,8 @@ cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 template <int KM, int AR>
 cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, bool* handled)
 {
-    if (cfg == 0) return launch_rr<KM, AR, 32, 8, 4>(cx, p, handled);
-    if (cfg == 2) return launch_rr<KM, AR, 32, 8, 5>(cx, p, handled);
-    return launch_rr<KM, AR, 32, 4, 4>(cx, p, handled);
+    if (cfg == 1) return launch_rr<KM, AR, 32, 8, 6>(cx, p, handled);
+    return launch_rr<KM, AR, 32, 8, 5>(cx, p, handled);
 }
 
 }  // namespace
@@ -439,8 +430,7 @@ cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, b
 // f_{l+1}(coarse interior planes [zcb, zce)) = R(f_l - A_l v_l); the fine level must hold v planes
 // 2*Zc-2 .. 2*Zc+2 of every coarse plane Zc it is asked for
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
-                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, double* vzero,
-                              bool* handled)
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled)
 {
     *handled = false;
     int cfg = 0;
@@ -449,9 +439,9 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& g
         if (gc.nx < 24 || gc.ny < 8 || zce - zcb < 4) return cudaSuccess;  // small levels: unfused simple kernels
         cfg = cx.tune.rr_variant;
     }
-    ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse, vzero};
+    ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse};
     cudaError_t e = cudaSuccess;
-    for (int c = v ? cfg : 0; c <= (v ? cfg : 2) && e == cudaSuccess; c++) {
+    for (int c = v ? cfg : 0; c <= (v ? cfg : 1) && e == cudaSuccess; c++) {
 #define CALL(KMV) AR_SWITCH(ar, e = (dispatch_rr<KMV, ARV>(cx, p, c, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;
@@ -476,7 +466,7 @@ cudaError_t kt_prepare()
     cudaError_t e = cudaSuccess;
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
         for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
-            e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nullptr, &handled);
+            e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_prolong_occ, prolong_correct_zmarch, PBX * PBY, 0);
     done = e == cudaSuccess;
     return e;
