@@ -311,7 +311,7 @@ def main():
     if os.path.exists(tpath) and n == REF_GRID:
         with open(tpath) as f:
             traffic = json.load(f).get(("smooth2_n%d" if per_launch > 1.5 else "smooth_n%d") % n[0], None)
-    kname = ("smooth2_tma: two damped-Jacobi sweeps per pass (temporal blocking)" if per_launch > 1.5
+    kname = ("smooth2u_tma: two damped-Jacobi sweeps per pass (temporal blocking, z-march unrolled over the ring period)" if per_launch > 1.5
              else "stencil_tma: one damped-Jacobi sweep per pass")
     roofline = {"bound": "hbm", "kernel": "fine-level smoother (level 0, inside the V-cycle) - " + kname, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,

@@ -237,6 +237,7 @@ __device__ __forceinline__ double lds_f64(uint32_t a)
     return v;
 }
 __device__ __forceinline__ void sts_f64(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // consumer-only barrier (named barrier 2) for kernels whose producer warp runs ahead
 template <int NT>
 __device__ __forceinline__ void consumer_sync()

@@ -245,6 +245,15 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
             // prefetch f / aux of the next plane (there is one while t < 2*nzc): requested before the wait for the v
             // plane, so the wait is part of its lead time
             double2 nf1 = zero2, nf2 = zero2, na1 = zero2, na2 = zero2;
+            if (t + 1 < 2 * nzc) {  // and the plane after it into L2: one plane of lead does not cover the HBM latency
+                const i64 cp = c0 + (i64)(t + 2) * plane;
+                if (ld1) prefetch_l2(p.f + cp);
+                if (ld2) prefetch_l2(p.f + cp + pitch);
+                if (KM >= KM_NEWTON_EXP) {
+                    if (ld1) prefetch_l2(p.aux + cp);
+                    if (ld2) prefetch_l2(p.aux + cp + pitch);
+                }
+            }
             if (t < 2 * nzc) {
                 const i64 cn = c0 + (i64)(t + 1) * plane;
                 if (ld1) nf1 = __ldg(reinterpret_cast<const double2*>(p.f + cn));
