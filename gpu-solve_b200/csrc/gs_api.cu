@@ -63,6 +63,7 @@ struct Level {
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
     bool coef_valid;
     int gv;           // slabs: ghost planes of v that are current on each side (0..2); refreshed lazily by need_v_halo
+    bool vzero_next;  // enqueue_vcycle: v is to be zeroed before the pre-smoothing that follows (done inside its first pass if possible)
     int pre_valid;    // vtmp == this many Jacobi sweeps of v for the current f/aux (written by the fused sweep+norm kernels)
 };
 
@@ -83,7 +84,7 @@ struct gs_handle {
     LaunchCtx cx;
     double* h_norm;  // pinned
     uint64_t launches;
-    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi;
+    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi, opt_vzero;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
     std::map<uint64_t, int> graphs_pre_valid;      // lev[0].pre_valid after a replay of each graph
@@ -334,13 +335,30 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     L.pre_valid = 0;
     const double* aux = smoother_aux(h, level, km);
     const bool tuned = h->opt_kernels && h->canonical;
+    if (L.vzero_next) {
+        // CpuSolver.cpp:100-101 v.fill(0) followed by the pre-smoothing: the two-sweep kernel takes the zero iterate as a
+        // constant (no memset, no read of v); its output buffer becomes v, the stale one is only ever written again
+        L.vzero_next = false;
+        bool handled = false;
+        if (iters >= 2 && tuned && !partitioned(h, level))
+            CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, true, &handled));
+        if (handled) {
+            iters -= 2;
+            h->lvl_sweeps[level] += 2;
+            std::swap(L.v, L.vtmp);
+            L.gv = 0;
+        } else {
+            CU(cudaMemsetAsync(L.v, 0, L.count * sizeof(double), h->stream));
+            L.gv = 2;
+        }
+    }
     while (iters > 0) {
         bool handled = false;
         GS(need_v_halo(h, level, (iters >= 2 && tuned && h->cx.tune.fuse2) ? 2 : 1));
         if (iters >= 2 && tuned) {
             // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
             if (!partitioned(h, level) || L.gv >= 2)
-                CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, &handled));
+                CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, false, &handled));
             if (handled) {
                 iters -= 2;
                 h->lvl_sweeps[level] += 2;
@@ -399,7 +417,7 @@ int do_norm_residual(gs_handle* h)
         const double* aux = smoother_aux(h, 0, km);
         GS(need_v_halo(h, 0, (h->p.pre >= 2 && h->cx.tune.fuse2) ? 2 : 1));
         if (h->p.pre >= 2 && (!partitioned(h, 0) || L.gv >= 2)) {
-            CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, &handled));
+            CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, false, &handled));
             if (handled) {
                 L.pre_valid = 2;
                 return GS_OK;
@@ -534,8 +552,12 @@ int enqueue_vcycle(gs_handle* h)
     for (int i = 0; i < last; i++) {
         GS(do_smooth(h, i, h->p.pre));
         GS(do_restrict_residual(h, i));
-        if (h->p.mode != GS_MODE_NONLINEAR) GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));
-        else GS(do_fas_coarse_rhs(h, i));
+        if (h->p.mode != GS_MODE_NONLINEAR) {
+            if (h->opt_vzero && h->world == 1) {
+                h->lev[i + 1].vzero_next = true;  // consumed by the do_smooth that follows
+                h->lev[i + 1].pre_valid = 0;
+            } else GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));
+        } else GS(do_fas_coarse_rhs(h, i));
     }
     GS(do_smooth(h, last, h->p.pre + h->p.post));
     if ((h->p.pre + h->p.post) & 1) {  // restore buffer parity on the (tiny) coarsest level
@@ -567,6 +589,7 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
     key ^= (uint64_t)(h->lev[0].ar & 3) << 10;
     key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
+    key ^= (uint64_t)(h->opt_vzero & 1) << 8;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     // slabs: which ghost planes are current decides which exchanges the captured cycle contains
@@ -806,6 +829,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_graph = 1;
     h->opt_timing = 0;
     h->opt_fuse_norm = 1;
+    h->opt_vzero = 1;
     h->opt_graph_multi = 1;  // capture the NCCL halo exchanges of a slab V-cycle into the graph as well
     h->comm = nullptr;
     h->h_norm = nullptr;
@@ -1405,6 +1429,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->opt_fuse_norm = value != 0;
         h->lev[0].pre_valid = false;
     }
+    else if (n == "vzero") h->opt_vzero = value != 0;
     else if (n == "timing") h->opt_timing = value != 0;
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);

@@ -123,7 +123,8 @@ cudaError_t kx_prepare();
 // vout = S(S(vin)) on local planes [zb, ze); needs two valid planes of vin outside the range.  with_norm: also
 // sum of squares of the residual of vin -> cx.norm.result
 cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
-                       const double* vin, double* vout, const double* f, const double* aux, bool with_norm, bool* handled);
+                       const double* vin, double* vout, const double* f, const double* aux, bool with_norm, bool vzero,
+                       bool* handled);
 
 // ---- kernels_transfer.cu: tuned grid-transfer kernels (canonical stencil) ----
 cudaError_t kt_prepare();

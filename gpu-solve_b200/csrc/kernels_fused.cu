@@ -227,7 +227,9 @@ struct S2uCfg {
     static_assert(TY % 2 == 0 && NCONS % 32 == 0, "two rows per thread, whole warps");
 };
 
-template <int KM, int AR, bool NORM, int TY>
+// VZ: the input iterate is identically zero (first pre-smoothing pass on a coarse level, src/cpu/CpuSolver.cpp:100-101):
+// v is neither zeroed by a memset nor read — the taps are the constant 0.0, same arithmetic, same bits.
+template <int KM, int AR, bool NORM, int TY, bool VZ>
 __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __grid_constant__ CUtensorMap map_v,
                                                                       const __grid_constant__ CUtensorMap map_f, Fused2P p)
 {
@@ -250,11 +252,19 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
     auto issue = [&](int P, int S) {
         const bool has_f = P >= 1 && P <= last;
         const uint32_t bar = bars + S * 8, dst = sbase + S * Cfg::STAGE;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(Cfg::V_BYTES + (has_f ? Cfg::F_BYTES : 0))
+        if (VZ && !has_f) {
+            // nothing to load; the plain arrival completes the stage's phase so its parity stays in step with the plane count
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+            return;
+        }
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+                     "r"((VZ ? 0 : Cfg::V_BYTES) + (has_f ? Cfg::F_BYTES : 0))
                      : "memory");
-        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
-                     "l"(&map_v), "r"(bar), "r"(GS_XOFF + x0 - 2), "r"(y0 - 2), "r"(z0 - 2 + P)
-                     : "memory");
+        if (!VZ)
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+                             dst),
+                         "l"(&map_v), "r"(bar), "r"(GS_XOFF + x0 - 2), "r"(y0 - 2), "r"(z0 - 2 + P)
+                         : "memory");
         if (has_f)
             asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
                              dst + Cfg::V_BYTES),
@@ -304,13 +314,16 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
 #pragma unroll
     for (int i = 0; i < 2; i++) fq[i][0] = fq[i][1] = xq[i][0] = xq[i][1] = 0.0;
     double sq = 0.0;
-    mbar_wait_a(bars + 0, 0);
-    vq[0][0] = lds_f64(tb);
-    vq[0][1] = lds_f64(tb + ROW);
-    mbar_wait_a(bars + 8, 0);
-    vq[1][0] = lds_f64(tb + Cfg::STAGE);
-    vq[1][1] = lds_f64(tb + Cfg::STAGE + ROW);
-    vq[2][0] = vq[2][1] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; i++) vq[i][0] = vq[i][1] = 0.0;
+    if (!VZ) {
+        mbar_wait_a(bars + 0, 0);
+        vq[0][0] = lds_f64(tb);
+        vq[0][1] = lds_f64(tb + ROW);
+        mbar_wait_a(bars + 8, 0);
+        vq[1][0] = lds_f64(tb + Cfg::STAGE);
+        vq[1][1] = lds_f64(tb + Cfg::STAGE + ROW);
+    }
 
     // one plane: K = q mod 6 (ring stage, queue slots, parities), PH = 1 / 2 for the start-up planes q = 1 / 2, else 0
     auto step = [&](auto Kc, auto PHc, const int q, const uint32_t par) {
@@ -324,12 +337,17 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
             if (a1 && zok) xa = xp[0];
             if (b1 && zok) xb = xp[ab];
         }
-        mbar_wait_a(bars + SU * 8, SU == 0 ? par ^ 1u : par);
         const uint32_t c = tb + SC * Cfg::STAGE, u = tb + SU * Cfg::STAGE;
-        vq[iU][0] = lds_f64(u);
-        vq[iU][1] = lds_f64(u + ROW);
-        const double Ea = lds_f64(c + 8), Wa = lds_f64(c - 8), Sa = lds_f64(c - ROW);
-        const double Eb = lds_f64(c + ROW + 8), Wb = lds_f64(c + ROW - 8), Nb = lds_f64(c + 2 * ROW);
+        double Ea = 0.0, Wa = 0.0, Sa = 0.0, Eb = 0.0, Wb = 0.0, Nb = 0.0;
+        if (VZ) {
+            mbar_wait_a(bars + SC * 8, par);  // only the f box of plane q
+        } else {
+            mbar_wait_a(bars + SU * 8, SU == 0 ? par ^ 1u : par);
+            vq[iU][0] = lds_f64(u);
+            vq[iU][1] = lds_f64(u + ROW);
+            Ea = lds_f64(c + 8), Wa = lds_f64(c - 8), Sa = lds_f64(c - ROW);
+            Eb = lds_f64(c + ROW + 8), Wb = lds_f64(c + ROW - 8), Nb = lds_f64(c + 2 * ROW);
+        }
         fq[jC][0] = lds_f64(c + FOFF);
         fq[jC][1] = lds_f64(c + FOFF + ROW);
         xq[jC][0] = xa;
@@ -441,21 +459,23 @@ cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
     return cudaGetLastError();
 }
 
-template <int KM, int AR, bool NORM, int TY>
+template <int KM, int AR, bool NORM, int TY, bool VZ>
 cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
 {
     using Cfg = S2uCfg<TY>;
     static bool prepared = false;
     static int occ = 1;
     if (!prepared) {
-        cudaError_t e = cudaFuncSetAttribute(smooth2u_tma<KM, AR, NORM, TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smooth2u_tma<KM, AR, NORM, TY>, Cfg::THREADS, Cfg::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(smooth2u_tma<KM, AR, NORM, TY, VZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smooth2u_tma<KM, AR, NORM, TY, VZ>, Cfg::THREADS, Cfg::SMEM);
         if (e != cudaSuccess) return e;
         prepared = true;
     }
     if (!p.vin) return cudaSuccess;  // preparation call
     CUtensorMap mv, mf;
-    if (!gs_tensor_map(p.vin, p.g, Cfg::BW, Cfg::VH, &mv) || !gs_tensor_map(p.f, p.g, Cfg::BW, Cfg::FH, &mf)) return cudaSuccess;
+    if (!gs_tensor_map(p.f, p.g, Cfg::BW, Cfg::FH, &mf)) return cudaSuccess;
+    if (VZ) mv = mf;  // never dereferenced
+    else if (!gs_tensor_map(p.vin, p.g, Cfg::BW, Cfg::VH, &mv)) return cudaSuccess;
     const int tx = (p.g.nx + Cfg::TXO - 1) / Cfg::TXO, ty = (p.g.ny + TY - 1) / TY;
     const int planes = p.ze - p.zb;
     // every chunk re-reads four planes, recomputes two first-sweep planes and fills the ring
@@ -467,26 +487,32 @@ cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
     }
     dim3 grid(tx, ty, (planes + p.zchunk - 1) / p.zchunk);
     if (NORM && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;
-    smooth2u_tma<KM, AR, NORM, TY><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    smooth2u_tma<KM, AR, NORM, TY, VZ><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
     *handled = true;
     return cudaGetLastError();
 }
 
 template <int KM, int AR, bool NORM>
-cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool* handled)
+cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool vzero, bool* handled)
 {
     // the unrolled kernel spills heavily with exp() of the Newton iterate in the loop (KM_NEWTON_EXP, only reached
     // with the precomputed-coefficient path switched off): that mode keeps the rolled kernel
-    if (variant == 1 || KM == KM_NEWTON_EXP) return launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
-    return launch_s2u<KM, AR, NORM, 12>(cx, p, handled);
+    if (variant == 1 || KM == KM_NEWTON_EXP) return vzero ? cudaSuccess : launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
+    // the zero-input variant exists where the V-cycle zeroes the coarse iterate: modes 0 and 2, no norm wanted
+    if (vzero) {
+        if (!NORM && (KM == KM_LINEAR || KM == KM_NEWTON_COEF)) return launch_s2u<KM, AR, false, 12, true>(cx, p, handled);
+        return cudaSuccess;
+    }
+    return launch_s2u<KM, AR, NORM, 12, false>(cx, p, handled);
 }
 
 }  // namespace
 
 // vout = S(S(vin)); with_norm: also sum r(vin)^2 -> cx.norm.result.  The level must hold two valid
-// planes of vin and one of f (and aux) outside [zb, ze).
+// planes of vin and one of f (and aux) outside [zb, ze).  vzero: vin is to be taken as identically zero and is not read
+// (handled only by the unrolled kernel in modes 0 and 2 without norm).
 cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
-                       double* vout, const double* f, const double* aux, bool with_norm, bool* handled)
+                       double* vout, const double* f, const double* aux, bool with_norm, bool vzero, bool* handled)
 {
     *handled = false;
     if (vin) {
@@ -499,8 +525,8 @@ cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int z
     cudaError_t e = cudaSuccess;
     for (int var = lo; var <= hi && e == cudaSuccess; var++) {
 #define CALL(KMV)                                                                    \
-    AR_SWITCH(ar, e = with_norm ? (dispatch_s2<KMV, ARV, true>(cx, p, var, handled)) \
-                                : (dispatch_s2<KMV, ARV, false>(cx, p, var, handled)))
+    AR_SWITCH(ar, e = with_norm ? (dispatch_s2<KMV, ARV, true>(cx, p, var, vzero, handled)) \
+                                : (dispatch_s2<KMV, ARV, false>(cx, p, var, vzero, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;
         case KM_NONLINEAR: CALL(KM_NONLINEAR); break;
@@ -525,7 +551,8 @@ cudaError_t kx_prepare()
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
         for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
             for (int nm = 0; nm < 2 && e == cudaSuccess; nm++)
-                e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, &handled);
+                for (int vz = 0; vz < 2 && e == cudaSuccess; vz++)
+                    e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, vz != 0, &handled);
     done = e == cudaSuccess;
     return e;
 }
