@@ -84,7 +84,7 @@ struct gs_handle {
     LaunchCtx cx;
     double* h_norm;  // pinned
     uint64_t launches;
-    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi, opt_vzero;
+    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi, opt_vzero, opt_timers;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
     std::map<uint64_t, int> graphs_pre_valid;      // lev[0].pre_valid after a replay of each graph
@@ -688,6 +688,40 @@ int residual_norm_sync(gs_handle* h, int level, bool store_r, double* norm)
     return GS_OK;
 }
 
+int drain_events_impl(gs_handle* h)
+{
+    CU(cudaStreamSynchronize(h->stream));
+    for (auto& ep : h->ev_used) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, ep.a, ep.b) == cudaSuccess) {
+            h->op_ms[ep.op] += t;
+            h->lvl_ms[(size_t)ep.level * GS_OP_COUNT + ep.op] += t;
+        }
+        h->ev_free.push_back(ep.a);
+        h->ev_free.push_back(ep.b);
+    }
+    h->ev_used.clear();
+    return GS_OK;
+}
+
+// Timer::stop's partial timers (src/Timer.cpp:17-24): ", name: Nms (Cx) name: Nms (Cx) " after "Took Nms".  With
+// GPUSOLVE_TIMERS=1 the operators of the V-cycle are reported that way (CUDA-event time, plain launches instead of
+// the graph); "sumBuffer" — the SYCL backend's norm reduction that runExperiments.py:81-85 sums up — is part of the
+// residual kernels here and reported as 0ms.
+void print_partial_timers(gs_handle* h)
+{
+    static const char* names[GS_OP_COUNT] = {"smooth", "residual", "restrict", "prolong", "other"};
+    if (drain_events_impl(h) != GS_OK) return;
+    std::cout << ", ";
+    for (int op = 0; op < GS_OP_COUNT; op++) {
+        if (h->op_launches[op] == 0 && h->op_ms[op] == 0.0) continue;
+        std::cout << names[op] << ": " << (long long)(h->op_ms[op] + 0.5) << "ms (" << h->op_launches[op] << "x) ";
+    }
+    std::cout << "sumBuffer: 0ms (1x) ";
+    memset(h->op_ms, 0, sizeof h->op_ms);
+    memset(h->op_launches, 0, sizeof h->op_launches);
+}
+
 // CpuSolver::solve, src/cpu/CpuSolver.cpp:12-43
 int solve_mg(gs_handle* h, uint64_t maxiter, double tol, bool print, std::vector<double>* hist, uint64_t* cycles,
              bool* converged)
@@ -701,21 +735,36 @@ int solve_mg(gs_handle* h, uint64_t maxiter, double tol, bool print, std::vector
     if (hist) hist->push_back(initial);
     *cycles = 0;
     *converged = false;
+    const bool timers = print && h->opt_timers;
+    const int timing0 = h->opt_timing;
+    if (timers) {
+        h->opt_timing = 1;
+        drain_events_impl(h);
+        memset(h->op_ms, 0, sizeof h->op_ms);
+        memset(h->op_launches, 0, sizeof h->op_launches);
+    }
     for (uint64_t i = 0; i < maxiter; i++) {
         auto t0 = std::chrono::high_resolution_clock::now();
         double res;
-        GS(run_vcycle(h, &res));
+        int rc = run_vcycle(h, &res);
+        if (rc != GS_OK) {
+            h->opt_timing = timing0;
+            return rc;
+        }
         ++*cycles;
         if (hist) hist->push_back(res);
         if (print) {
             std::cout << "iter: " << i << " residual: " << res << ' ';
-            std::cout << "Took " << ms_since(t0) << "ms\n";  // src/Timer.cpp:13-27
+            std::cout << "Took " << ms_since(t0) << "ms";  // src/Timer.cpp:13-27
+            if (timers) print_partial_timers(h);
+            std::cout << '\n';
         }
         if (reached(res, initial, tol)) {
             *converged = true;
             break;
         }
     }
+    h->opt_timing = timing0;
     return GS_OK;
 }
 
@@ -830,6 +879,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_timing = 0;
     h->opt_fuse_norm = 1;
     h->opt_vzero = 1;
+    h->opt_timers = 0;
+    if (const char* e = getenv("GPUSOLVE_TIMERS")) h->opt_timers = atoi(e) != 0;
     h->opt_graph_multi = 1;  // capture the NCCL halo exchanges of a slab V-cycle into the graph as well
     h->comm = nullptr;
     h->h_norm = nullptr;
@@ -1370,21 +1421,7 @@ int gs_reset_timing(gs_handle* h)
     return GS_OK;
 }
 
-static int drain_events(gs_handle* h)
-{
-    CU(cudaStreamSynchronize(h->stream));
-    for (auto& ep : h->ev_used) {
-        float t = 0.f;
-        if (cudaEventElapsedTime(&t, ep.a, ep.b) == cudaSuccess) {
-            h->op_ms[ep.op] += t;
-            h->lvl_ms[(size_t)ep.level * GS_OP_COUNT + ep.op] += t;
-        }
-        h->ev_free.push_back(ep.a);
-        h->ev_free.push_back(ep.b);
-    }
-    h->ev_used.clear();
-    return GS_OK;
-}
+static int drain_events(gs_handle* h) { return drain_events_impl(h); }
 
 int gs_get_level_timing(gs_handle* h, int level, double ms[GS_OP_COUNT], uint64_t launches[GS_OP_COUNT])
 {
@@ -1430,6 +1467,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->lev[0].pre_valid = false;
     }
     else if (n == "vzero") h->opt_vzero = value != 0;
+    else if (n == "timers") h->opt_timers = value != 0;
     else if (n == "timing") h->opt_timing = value != 0;
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);

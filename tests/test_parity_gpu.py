@@ -138,6 +138,26 @@ def test_shipped_config_through_the_driver_binary(gs, golden):
     assert all(its) and [m.group(2) for m in its] == ["12.3816", "0.527004", "0.0222718", "0.00093763"]
 
 
+def test_driver_partial_timers_keep_the_experiment_script_regexes(gs, tmp_path):
+    """GPUSOLVE_TIMERS=1: Timer::stop's partial-timer tail (src/Timer.cpp:17-24) after "Took Nms"; the regexes of
+    runExperiments.py:46 and :81 must still match and the residuals must not change"""
+    import os
+    import re
+    import subprocess
+    conf = tmp_path / "lin.conf"
+    conf.write_text("3\n1e-30\n63 63 63\n0\n2\n2\n0.8\n1.0\n6 -1 -1 -1 -1 -1 -1\n0 1 -1 0 0 0 0\n0 0 0 1 -1 0 0\n0 0 0 0 0 1 -1\n")
+    outs = []
+    for timers in ("0", "1"):
+        r = subprocess.run([gs.EXE, str(conf)], capture_output=True, text=True, timeout=120, env=dict(os.environ, GPUSOLVE_TIMERS=timers))
+        assert r.returncode == 0, r.stderr
+        outs.append(r.stdout)
+    it = re.compile(r"iter: (\d+) residual: ([\d\.e-]+) Took (\d+)ms")
+    plain, timed = it.findall(outs[0]), it.findall(outs[1])
+    assert len(plain) == 3 and [m[:2] for m in plain] == [m[:2] for m in timed]
+    assert len(re.findall(r"sumBuffer: (\d+)ms", outs[1])) == 3 and "sumBuffer" not in outs[0]
+    assert re.search(r"Took \d+ms, smooth: \d+ms \(\d+x\) ", outs[1])
+
+
 def test_get_set_roundtrip_and_layouts(gs):
     dev = CudaBackend(gs, n=(5, 7, 6), mode=1)
     a = seeded_field(dev.shape(0), 7, interior_only=False)
