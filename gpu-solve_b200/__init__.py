@@ -90,6 +90,7 @@ SIGNATURES = {
     "gs_create_slab": (_i, [C.POINTER(Params), _i, _i, _i, _vp, C.POINTER(_vp)]),
     "gs_destroy": (_i, [_vp]),
     "gs_partition": (_i, [C.POINTER(Params), _i, _i, _i, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_i)]),
+    "gs_plan_zchunk": (_i, [_i, _i, _i, _i, _i, _i, _i, _i]),
     "gs_num_levels": (_i, [_vp]),
     "gs_get_level_info": (_i, [_vp, _i, C.POINTER(_u64 * 3), _dp]),
     "gs_get_field": (_i, [_vp, _i, _i, _vp, _i]),
@@ -148,6 +149,13 @@ def partition(params, world, rank, level):
     zb, ze, rep = C.c_uint64(), C.c_uint64(), C.c_int()
     _check(load().gs_partition(C.byref(params), world, rank, level, C.byref(zb), C.byref(ze), C.byref(rep)))
     return zb.value, ze.value, rep.value
+
+
+def plan_zchunk(tiles, planes, sm_count=148, ctas_per_sm=2, overhead=6, min_chunk=16, max_chunk=128, even=False):
+    rc = load().gs_plan_zchunk(tiles, planes, sm_count, ctas_per_sm, overhead, min_chunk, max_chunk, int(even))
+    if rc < 0:
+        _check(rc)
+    return rc
 
 
 def comm_unique_id():

@@ -20,6 +20,9 @@
 #include "gs_comm.h"
 #include "gs_internal.h"
 
+int gs_pick_zchunk_waves(const LaunchCtx& cx, int tiles, int planes, int ctas_per_sm, int overhead, int min_chunk, int max_chunk,
+                         bool even);
+
 // ---------------------------------------------------------------------------------
 // errors
 // ---------------------------------------------------------------------------------
@@ -1128,6 +1131,14 @@ int gs_partition(const gs_params* p, int world, int rank, int level, uint64_t* z
     }
     if (replicated_from) *replicated_from = P.replicated_from;
     return GS_OK;
+}
+
+int gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int overhead, int min_chunk, int max_chunk, int even)
+{
+    if (tiles < 1 || planes < 1 || sm_count < 1 || min_chunk < 1 || max_chunk < min_chunk) return fail(GS_EINVAL, "bad chunk-plan arguments");
+    LaunchCtx cx{};
+    cx.sm_count = sm_count;
+    return gs_pick_zchunk_waves(cx, tiles, planes, ctas_per_sm, overhead, min_chunk, max_chunk, even != 0);
 }
 
 int gs_num_levels(const gs_handle* h) { return h ? (int)h->lev.size() : fail(GS_EINVAL, "null handle"); }

@@ -1,7 +1,8 @@
 // kernels_fused.cu — temporally blocked smoother for sm_100a (canonical 7-point stencil):
 // TWO damped-Jacobi sweeps per pass over the level.
 //
-//   smooth2_tma   v'' = S(S(v))   (src/cpu/CpuSolver.cpp:141-179 applied twice)
+//   smooth2u_tma  v'' = S(S(v))   (src/cpu/CpuSolver.cpp:141-179 applied twice), plane loop unrolled over the period
+//                 of its rings (the kernel the V-cycle uses); smooth2_tma is the same algorithm with a rolled loop.
 //                 24 B per lattice point for two sweeps (read v, read f, write v''), i.e.
 //                 12 B per lattice update instead of 24.
 //
@@ -9,13 +10,18 @@
 // v, src/cpu/CpuSolver.cpp:149-177), so the second sweep of a point may run as soon as the
 // first sweep of its seven neighbours is known.  A CTA owns a 60 x TY output tile, marches
 // along z and keeps a two-deep wavefront:
-//   * one producer warp streams the v tile with a two-cell rim (64 x (TY+4) box) and the f tile
-//     with a one-cell rim (64 x (TY+2) box) of every plane into a shared-memory ring with TMA
-//     (cp.async.bulk.tensor.3d, full/empty mbarriers);
-//   * a consumer thread owns two y-adjacent columns of the 62 x (TY+2) first-sweep region with
+//   * the v tile with a two-cell rim (64 x (TY+4) box) and the f tile with a one-cell rim
+//     (64 x (TY+2) box) of every plane arrive in a shared-memory ring by TMA
+//     (cp.async.bulk.tensor.3d, one "full" mbarrier per stage).  There is no producer warp:
+//     thread 0 issues the load of plane q+NSTAGE-1 once the split-phase barrier below has told it
+//     that every warp is done with plane q-1;
+//   * a thread owns two y-adjacent columns of the 62 x (TY+2) first-sweep region with
 //     register queues along z for the input and for the first-sweep values of its own columns;
 //     first-sweep planes go through a two-slot shared-memory ring so that the in-plane
-//     neighbours of the second sweep can be read one plane later (one named barrier per plane);
+//     neighbours of the second sweep can be read one plane later.  The ring is guarded by ONE
+//     split-phase mbarrier instead of a CTA barrier per plane: a warp arrives after storing its
+//     first-sweep plane and waits only after the next plane's first sweep, so slow warps have
+//     most of a plane of slack;
 //   * first-sweep values outside the interior are forced to zero — what the unfused path reads
 //     from the halo of the ping-pong buffer.
 // Per-point arithmetic is point_update of kernels_fast.cu (canon_residual + jacobi_update,

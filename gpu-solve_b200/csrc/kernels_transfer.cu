@@ -120,9 +120,9 @@ __global__ void __launch_bounds__(PBX* PBY) prolong_correct_zmarch(ProlongFastP 
 // ---------------------------------------------------------------------------------
 // A CTA owns CX x CY coarse columns and marches along coarse z.  Coarse point (X,Y,Z) needs the
 // residual at the 27 fine points (2X+ii, 2Y+jj, 2Z+kk); every fine residual needs its 7 v taps.
-//   * one producer warp streams fine v planes (xy box of the tile plus rim) into a shared-memory
-//     ring with TMA; f (and the Newton coefficient) are read straight from global memory, one
-//     plane ahead, as aligned double2.
+//   * fine v planes (xy box of the tile plus rim) arrive in a shared-memory ring by TMA, issued by
+//     thread 0 after each coarse plane's CTA barrier; f (and the Newton coefficient) are read straight
+//     from global memory as aligned double2, one plane ahead into registers and two planes ahead into L2.
 //   * compute thread (X,Y) owns the 2x2 fine columns x in {2X-1, 2X}, y in {2Y-1, 2Y} with a
 //     register queue along z; "strip" threads own the single columns of the extra fine column
 //     x = 2(X0+CX)-1 and row y = 2(Y0+CY)-1 that the last coarse column/row of the tile needs

@@ -123,6 +123,12 @@ int  gs_destroy(gs_handle* h);
 int  gs_partition(const gs_params* p, int world, int rank, int level,
                   uint64_t* z_begin, uint64_t* z_end, int* replicated_from);
 
+/* z-chunk length the z-marching kernels use for `planes` planes of a level cut into `tiles` xy tiles, pure host
+ * arithmetic (no GPU): the chunk count that minimises (waves of sm_count * ctas_per_sm resident CTAs) x (chunk +
+ * overhead planes), so grids fill whole waves.  Introspection for tests and tuning; returns the chunk (>= 1). */
+int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int overhead,
+                    int min_chunk, int max_chunk, int even);
+
 /* ---- introspection: CpuGridData::numLevels / getLevel (src/cpu/CpuGridData.h:22-33) */
 int  gs_num_levels(const gs_handle* h);
 int  gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hval);

@@ -130,3 +130,40 @@ def test_partition_world1_and_small_grids_are_unpartitioned(gs):
     for n, world in ((31, 1), (7, 8)):
         zb, ze, rep = gs.partition(gs.make_params(n), world, 0, 0)
         assert (zb, ze, rep) == (0, n + 2, 0)
+
+
+@pytest.mark.parametrize("tiles,planes,occ,overhead,lo,hi,even", [
+    (387, 511, 2, 6, 16, 128, False),     # smooth2u at 513^3
+    (110, 255, 2, 6, 16, 128, False),     # ... at 257^3
+    (256, 255, 2, 3, 4, 64, False),       # resid+restrict at 513^3 (coarse planes)
+    (256, 511, 4, 2, 8, 128, True),       # prolongation at 513^3
+    (4, 31, 2, 3, 4, 64, False),          # a small level
+    (1, 1, 1, 0, 1, 1, False),
+])
+def test_zchunk_plan_fills_whole_waves(gs, tiles, planes, occ, overhead, lo, hi, even):
+    """grid sizing of the z-marching kernels (gs_plan_zchunk): the chunk respects its bounds and parity, and no other
+    admissible chunk count gives fewer waves x (chunk + overhead)"""
+    sm = 148
+    chunk = gs.plan_zchunk(tiles, planes, sm, occ, overhead, lo, hi, even)
+    assert 1 <= chunk <= max(min(hi, planes), 1) + (1 if even else 0)
+    assert chunk >= min(lo, planes) or chunk == planes
+    if even:
+        assert chunk % 2 == 0
+
+    def cost(c):
+        nch = -(-planes // c)
+        waves = -(-tiles * nch // (sm * occ))
+        return waves * (c + overhead)
+
+    best = cost(chunk)
+    for n in range(1, planes + 1):
+        c = -(-planes // n)
+        if even:
+            c += c & 1
+        if c > min(hi, planes) or c < min(lo, min(hi, planes)):
+            continue
+        assert best <= cost(c), f"chunk {c} would be cheaper than {chunk}"
+    # the headline launch: 513^3 smoother grid is within 2 % of a whole number of waves
+    if (tiles, planes) == (387, 511):
+        ctas = tiles * -(-planes // chunk)
+        assert ctas / (sm * occ) > 0.97 * -(-ctas // (sm * occ))
