@@ -87,7 +87,7 @@ struct gs_handle {
     LaunchCtx cx;
     double* h_norm;  // pinned
     uint64_t launches;
-    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi, opt_vzero, opt_timers;
+    int opt_kernels, opt_graph, opt_timing, opt_fuse_norm, opt_graph_multi, opt_vzero, opt_timers, opt_unit, opt_rcp_div;
     std::map<uint64_t, cudaGraphExec_t> graphs;
     std::map<uint64_t, uint64_t> graphs_launches;  // kernels per replay of each graph
     std::map<uint64_t, int> graphs_pre_valid;      // lev[0].pre_valid after a replay of each graph
@@ -141,6 +141,14 @@ struct OpScope {  // CUDA-event bracket around one operator when "timing" is on
         return e;
     }
 };
+
+// arithmetic flags of a level for the tuned kernels (gs_device.cuh AR_*)
+int level_ar(const Level& L, bool unit_ok, bool rcp_ok)
+{
+    const int u = (L.unit && unit_ok) ? 2 : 0;
+    if (L.pow2) return 1 | u;
+    return rcp_ok ? (4 | u) : 0;
+}
 
 int num_levels_for(const gs_params& p)
 {
@@ -591,6 +599,7 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->cx.tune.fuse2 & 7) << 12;
     key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
     key ^= (uint64_t)(h->lev[0].ar & 3) << 10;
+    key ^= (uint64_t)(h->lev[0].ar & 4) << 4;
     key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
     key ^= (uint64_t)(h->opt_vzero & 1) << 8;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
@@ -882,6 +891,9 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_timing = 0;
     h->opt_fuse_norm = 1;
     h->opt_vzero = 1;
+    h->opt_unit = 1;
+    h->opt_rcp_div = 1;
+    if (const char* e = getenv("GPUSOLVE_RCP_DIV")) h->opt_rcp_div = atoi(e) != 0;
     h->opt_timers = 0;
     if (const char* e = getenv("GPUSOLVE_TIMERS")) h->opt_timers = atoi(e) != 0;
     h->opt_graph_multi = 1;  // capture the NCCL halo exchanges of a slab V-cycle into the graph as well
@@ -947,11 +959,11 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
         for (int i = 0; i < 7; i++) k.c[i] = p->stencil_val[i];
         k.hh = L.h * L.h;
         L.pow2 = is_pow2(k.hh);
-        k.inv_hh = L.pow2 ? 1.0 / k.hh : 0.0;
+        k.inv_hh = 1.0 / k.hh;
         bool unit = true;
         for (int i = 1; i < 7; i++) unit = unit && p->stencil_val[i] == -1.0;
         L.unit = unit;
-        L.ar = (L.pow2 ? 1 : 0) | (unit ? 2 : 0);
+        L.ar = level_ar(L, true, h->opt_rcp_div != 0);
         k.alpha = (L.h * L.h) / p->stencil_val[0];   // src/cpu/CpuSolver.cpp:145
         k.preFac = p->stencil_val[0] / (L.h * L.h);  // :144
         k.omega = p->omega;
@@ -1477,7 +1489,10 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->opt_fuse_norm = value != 0;
         h->lev[0].pre_valid = false;
     }
-    else if (n == "vzero") h->opt_vzero = value != 0;
+    else if (n == "rcp_div") {  // 0: true fp64 divide by h*h on levels where it is not a power of two (same bits, slower)
+        h->opt_rcp_div = value != 0;
+        for (auto& L : h->lev) L.ar = level_ar(L, h->opt_unit != 0, h->opt_rcp_div != 0);
+    } else if (n == "vzero") h->opt_vzero = value != 0;
     else if (n == "timers") h->opt_timers = value != 0;
     else if (n == "timing") h->opt_timing = value != 0;
     else if (n == "smooth_variant") h->cx.tune.smooth_variant = (int)value;
@@ -1485,7 +1500,8 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
-        for (auto& L : h->lev) L.ar = (L.pow2 ? 1 : 0) | ((L.unit && value != 0) ? 2 : 0);
+        h->opt_unit = value != 0;
+        for (auto& L : h->lev) L.ar = level_ar(L, h->opt_unit != 0, h->opt_rcp_div != 0);
     } else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
     else if (n == "fuse2") {
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));

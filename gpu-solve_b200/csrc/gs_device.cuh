@@ -30,27 +30,53 @@ int gs_pick_zchunk_waves(const LaunchCtx& cx, int tiles, int planes, int ctas_pe
 //   AR_POW2  h*h is a power of two: s * (1/hh) == s / hh exactly
 //   AR_UNIT  the six off-centre stencil values are exactly -1: s + (-1.0)*v == s - v exactly (IEEE: a - b is
 //            a + (-b), and -1.0*v is v with the sign flipped), so the six multiplies are dropped
-// Instantiated combinations: 0 (general), AR_POW2, AR_POW2|AR_UNIT; a level with unit taps but a non-power-of-two
-// h*h runs the general code (its fp64 divide dominates anyway).
-enum { AR_POW2 = 1, AR_UNIT = 2 };
-#define AR_SWITCH(ar, STMT)                                  \
-    do {                                                     \
-        if ((ar) == (AR_POW2 | AR_UNIT)) {                   \
-            constexpr int ARV = AR_POW2 | AR_UNIT;           \
-            STMT;                                            \
-        } else if ((ar) & AR_POW2) {                         \
-            constexpr int ARV = AR_POW2;                     \
-            STMT;                                            \
-        } else {                                             \
-            constexpr int ARV = 0;                           \
-            STMT;                                            \
-        }                                                    \
+//   AR_RCP   any other h*h: the quotient is formed from y = RN(1/hh) (host division, correctly rounded) by
+//            q0 = RN(s*y), then twice r = fma(-hh, q, s) [exact], q = fma(r, y, q).  q0 is within 2 ulp of s/hh, the first
+//            correction brings it within 1 ulp, and by Markstein's theorem (y correctly rounded, q within 1 ulp, exact
+//            remainder) the second yields RN(s/hh) — the bits of the fp64 divide for 5 instructions instead of ~25
+//            (tests/test_rcp_division.py checks the sequence against the divide for every h a grid up to 4096 can have).
+// Instantiated combinations: 0 (general: true divide), AR_POW2, AR_POW2|AR_UNIT, AR_RCP, AR_RCP|AR_UNIT.
+enum { AR_POW2 = 1, AR_UNIT = 2, AR_RCP = 4 };
+#define AR_SWITCH(ar, STMT)                                                     \
+    do {                                                                        \
+        const int ar_ = (ar);                                                   \
+        if (ar_ == (AR_POW2 | AR_UNIT)) {                                       \
+            constexpr int ARV = AR_POW2 | AR_UNIT;                              \
+            STMT;                                                               \
+        } else if (ar_ & AR_POW2) {                                             \
+            constexpr int ARV = AR_POW2;                                        \
+            STMT;                                                               \
+        } else if (ar_ == (AR_RCP | AR_UNIT)) {                                 \
+            constexpr int ARV = AR_RCP | AR_UNIT;                               \
+            STMT;                                                               \
+        } else if (ar_ & AR_RCP) {                                              \
+            constexpr int ARV = AR_RCP;                                         \
+            STMT;                                                               \
+        } else {                                                                \
+            constexpr int ARV = 0;                                              \
+            STMT;                                                               \
+        }                                                                       \
     } while (0)
+
+// s / (h*h) under the level's arithmetic flags; every branch returns the same bits
+template <int AR>
+__device__ __forceinline__ double div_hh(double s, const PointK& k)
+{
+    if (AR & AR_POW2) return s * k.inv_hh;
+    if (AR & AR_RCP) {
+        double q = s * k.inv_hh;
+        double r = __fma_rn(-k.hh, q, s);
+        q = __fma_rn(r, k.inv_hh, q);
+        r = __fma_rn(-k.hh, q, s);
+        return __fma_rn(r, k.inv_hh, q);
+    }
+    return s / k.hh;
+}
 
 template <int KM, int AR>
 __device__ __forceinline__ double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
 {
-    s = (AR & AR_POW2) ? s * k.inv_hh : s / k.hh;
+    s = div_hh<AR>(s, k);
     den = 0.0;
     if (KM == KM_NONLINEAR) {
         double ex = exp(vc);

@@ -37,7 +37,7 @@ __host__ __device__ __forceinline__ i64 gs_idx(const Geom& g, int x, int y, int 
 struct PointK {
     double c[7];     // stencil values, config order
     double hh;       // level.h * level.h
-    double inv_hh;   // 1/hh, only used when hh is a power of two (then s*inv_hh == s/hh bit for bit)
+    double inv_hh;   // RN(1/hh): s*inv_hh == s/hh bit for bit when hh is a power of two, else the seed of the corrected quotient (AR_RCP)
     double alpha;    // (h*h)/c[0]
     double preFac;   // c[0]/(h*h)
     double omega, gamma;

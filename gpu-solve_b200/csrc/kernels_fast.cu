@@ -443,7 +443,7 @@ cudaError_t kf_prepare()
     cudaError_t e = cudaSuccess;
     const int variants[] = {1, 13, 2, 21, 22};
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
-        for (int pw = 0; pw < 4 && e == cudaSuccess; pw++) {
+        for (int pw = 0; pw < 8 && e == cudaSuccess; pw++) {
             for (int var : variants) {
                 cx.tune.smooth_variant = var;
                 if (e == cudaSuccess) e = kf_smooth(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);

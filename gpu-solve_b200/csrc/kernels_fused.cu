@@ -555,7 +555,7 @@ cudaError_t kx_prepare()
     bool handled;
     cudaError_t e = cudaSuccess;
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
-        for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
+        for (int pw = 0; pw < 8 && e == cudaSuccess; pw++)
             for (int nm = 0; nm < 2 && e == cudaSuccess; nm++)
                 for (int vz = 0; vz < 2 && e == cudaSuccess; vz++)
                     e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, vz != 0, &handled);

@@ -474,7 +474,7 @@ cudaError_t kt_prepare()
     bool handled;
     cudaError_t e = cudaSuccess;
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
-        for (int pw = 0; pw < 4 && e == cudaSuccess; pw++)
+        for (int pw = 0; pw < 8 && e == cudaSuccess; pw++)
             e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_prolong_occ, prolong_correct_zmarch, PBX * PBY, 0);
     done = e == cudaSuccess;
