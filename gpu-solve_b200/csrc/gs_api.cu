@@ -1011,7 +1011,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->cx.tune.wave = 1;
     if (const char* ev = getenv("GPUSOLVE_WAVE")) h->cx.tune.wave = atoi(ev) != 0;
     if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(2, atoi(ev)));
-    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = atoi(ev) != 0;
+    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = std::max(0, std::min(2, atoi(ev)));
     e = kf_prepare();
     if (e == cudaSuccess) e = kt_prepare();
     if (e == cudaSuccess) e = kx_prepare();
@@ -1502,7 +1502,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;
         for (auto& L : h->lev) L.ar = level_ar(L, h->opt_unit != 0, h->opt_rcp_div != 0);
-    } else if (n == "rr_variant") h->cx.tune.rr_variant = value != 0;
+    } else if (n == "rr_variant") h->cx.tune.rr_variant = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
     else if (n == "fuse2") {
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
         h->lev[0].pre_valid = 0;

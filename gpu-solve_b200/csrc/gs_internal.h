@@ -63,7 +63,7 @@ struct Tune {
     int smooth_variant;  // 0 simple, 1x z-march through L1, 2x TMA-staged z-march (kernels_fast.cu)
     int zchunk;          // planes per CTA of the z-marching kernels
     int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
-    int rr_variant;      // fused residual+restriction kernel: 0 = five-stage ring, 1 = six-stage
+    int rr_variant;      // fused residual+restriction kernel: 0 = five-stage ring, 1 = six-stage (default), 2 = split-phase barrier (prepared, unvalidated)
     int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1 = five-stage ring, 2 = four-stage
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
     int zchunk2;         // planes per CTA of the two-sweep kernel
