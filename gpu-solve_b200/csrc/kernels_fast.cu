@@ -238,9 +238,7 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
 
     double sq = 0.0;
     mbar_wait(&full[0], 0);
-    double D = vbox(0)[ctr];
-    __syncwarp();
-    if (lane0) mbar_arrive(&empty[0]);
+    double D = vbox(0)[ctr];  // (stage 0 is released at the end of the first iteration, once D has been used)
     mbar_wait(&full[1 % NSTAGE], (1 / NSTAGE) & 1);
     double C = vbox(1)[ctr];
 
@@ -251,8 +249,6 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
         const double U = vbox(q + 1)[ctr];
         const double E = vb[ctr + 1], W = vb[ctr - 1], N = vb[ctr + Cfg::VW], S = vb[ctr - Cfg::VW];
         const double fv = fbox(q)[ty * TX + tx];
-        __syncwarp();
-        if (lane0) mbar_arrive(&empty[q % NSTAGE]);
         if (OP == OP_SMOOTH) {
             const double nv = point_update<KM, AR>(C, E, W, N, S, U, D, fv, aux, p.k);
             if (live) p.vout[c] = nv;
@@ -270,6 +266,14 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
                 if (p.vout) p.vout[c] = r;
                 sq += r * r;  // per-thread running sum in plane order: deterministic
             }
+        }
+        // release the stage of plane q only now, after the arithmetic above has consumed everything that was loaded from
+        // it: the arrival is then ordered behind the completion of those shared-memory loads by data dependence, not just
+        // by issue order (a ring refilled under a slow warp is what broke the producer-warp residual+restriction kernel)
+        __syncwarp();
+        if (lane0) {
+            if (q == 1) mbar_arrive(&empty[0]);
+            mbar_arrive(&empty[q % NSTAGE]);
         }
         D = C;
         C = U;
