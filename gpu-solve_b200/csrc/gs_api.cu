@@ -105,6 +105,7 @@ struct gs_handle {
     int replicated_from;
     double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
     size_t stage_count;
+    TailRec* tail;        // recorder of the coarse tail (cx.tune.tail_points > 0), made on first use
 };
 
 namespace {
@@ -345,7 +346,7 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     }
     L.pre_valid = 0;
     const double* aux = smoother_aux(h, level, km);
-    const bool tuned = h->opt_kernels && h->canonical;
+    const bool tuned = h->opt_kernels && h->canonical && !h->cx.rec;  // the tail records the one-thread-per-point operators
     if (L.vzero_next) {
         // CpuSolver.cpp:100-101 v.fill(0) followed by the pre-smoothing: the two-sweep kernel takes the zero iterate as a
         // constant (no memset, no read of v); its output buffer becomes v, the stale one is only ever written again
@@ -359,7 +360,7 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
             std::swap(L.v, L.vtmp);
             L.gv = 0;
         } else {
-            CU(cudaMemsetAsync(L.v, 0, L.count * sizeof(double), h->stream));
+            CU(ks_zero(h->cx, L.v, L.count));
             L.gv = 2;
         }
     }
@@ -407,7 +408,7 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     OpScope t(h, GS_OP_RESIDUAL, level);
     GS(need_v_halo(h, level, 1));
     bool handled = false;
-    if (h->opt_kernels && h->canonical)
+    if (h->opt_kernels && h->canonical && !h->cx.rec)
         CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled));
     if (!handled)
         CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
@@ -498,7 +499,7 @@ int do_restrict_residual(gs_handle* h, int level)
     }
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
-    if (h->opt_kernels && h->canonical) {
+    if (h->opt_kernels && h->canonical && !h->cx.rec) {
         // fused: the residual never goes to memory (kernels_transfer.cu)
         int czb, cze;
         coarse_range(h, level, &czb, &cze);
@@ -540,7 +541,7 @@ int do_prolong_correct(gs_handle* h, int level)
     // field out of place in that case keeps the buffer parity (and the CUDA graph) fixed
     const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
     bool handled = false;
-    if (h->opt_kernels) CU(kt_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, &handled));
+    if (h->opt_kernels && !h->cx.rec) CU(kt_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, &handled));
     if (!handled) CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
     if (flip) std::swap(F.v, F.vtmp);
     F.gv = 0;
@@ -551,16 +552,44 @@ int zero_field(gs_handle* h, Level& L, double* a)
 {
     L.pre_valid = false;
     OpScope t(h, GS_OP_OTHER, (int)(&L - h->lev.data()));
-    CU(cudaMemsetAsync(a, 0, L.count * sizeof(double), h->stream));
+    CU(ks_zero(h->cx, a, L.count));
     if (a == L.v) L.gv = 2;  // ghost planes included
     return GS_OK;
 }
 
+// first level of the coarse tail (run as one single-CTA kernel, kernels_simple.cu ks_tail_*), or -1.  Never the
+// coarsest level alone (nothing to merge), not on slabs, not while per-operator events are wanted.
+int tail_first_level(const gs_handle* h)
+{
+    if (h->cx.tune.tail_points <= 0 || h->world != 1 || h->opt_timing) return -1;
+    const int last = (int)h->lev.size() - 1;
+    for (int l = 0; l < last; l++) {
+        const Geom& g = h->lev[l].g;
+        if ((i64)g.nx * g.ny * g.nz <= (i64)h->cx.tune.tail_points) return l;
+    }
+    return -1;
+}
+
+int tail_begin(gs_handle* h)
+{
+    if (!h->tail) h->tail = ks_tail_new();
+    ks_tail_begin(h->cx, h->tail);
+    return GS_OK;
+}
+
+int tail_end(gs_handle* h)
+{
+    cudaError_t e = ks_tail_end(h->cx);
+    if (e != cudaSuccess) return fail(GS_ECUDA, "coarse-tail kernel: %s", cudaGetErrorString(e));
+    return GS_OK;
+}
+
 // everything CpuSolver::vcycle (src/cpu/CpuSolver.cpp:85-139) does, queued on the stream
-int enqueue_vcycle(gs_handle* h)
+int enqueue_vcycle_ops(gs_handle* h, int tail)
 {
     const int last = (int)h->lev.size() - 1;
     for (int i = 0; i < last; i++) {
+        if (i == tail) GS(tail_begin(h));  // from here down to the coarsest level and back up to this level: recorded
         GS(do_smooth(h, i, h->p.pre));
         GS(do_restrict_residual(h, i));
         if (h->p.mode != GS_MODE_NONLINEAR) {
@@ -573,16 +602,26 @@ int enqueue_vcycle(gs_handle* h)
     GS(do_smooth(h, last, h->p.pre + h->p.post));
     if ((h->p.pre + h->p.post) & 1) {  // restore buffer parity on the (tiny) coarsest level
         Level& L = h->lev[last];
-        CU(cudaMemcpyAsync(L.vtmp, L.v, L.count * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        CU(ks_copy(h->cx, L.vtmp, L.v, L.count));
         std::swap(L.v, L.vtmp);
     }
     for (int i = last; i > 0; i--) {
         GS(do_prolong_correct(h, i - 1));
         GS(do_smooth(h, i - 1, h->p.post));
+        if (i - 1 == tail) GS(tail_end(h));
     }
     GS(do_norm_residual(h));
     GS(norm_to_host(h, 0));
     return GS_OK;
+}
+
+int enqueue_vcycle(gs_handle* h)
+{
+    const int rc = enqueue_vcycle_ops(h, tail_first_level(h));
+    if (h->cx.rec) {  // an operator failed while recording: drop the program, never leave the recorder attached
+        h->cx.rec = nullptr;
+    }
+    return rc;
 }
 
 uint64_t parity_key(const gs_handle* h)
@@ -602,6 +641,7 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->lev[0].ar & 4) << 4;
     key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
     key ^= (uint64_t)(h->opt_vzero & 1) << 8;
+    key ^= (uint64_t)(tail_first_level(h) + 1) * 0xD6E8FEB86659FD93ull;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     // slabs: which ghost planes are current decides which exchanges the captured cycle contains
@@ -901,6 +941,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->h_norm = nullptr;
     h->stage = nullptr;
     h->stage_count = 0;
+    h->tail = nullptr;
+    h->cx.rec = nullptr;
     memset(h->op_ms, 0, sizeof h->op_ms);
     memset(h->op_launches, 0, sizeof h->op_launches);
     for (int i = 0; i < 7; i++) {
@@ -1012,6 +1054,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* ev = getenv("GPUSOLVE_WAVE")) h->cx.tune.wave = atoi(ev) != 0;
     if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(2, atoi(ev)));
     if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = std::max(0, std::min(2, atoi(ev)));
+    h->cx.tune.tail_points = 0;  // coarse tail as one single-CTA kernel: prepared, off until it has been through the GPU suite
+    if (const char* ev = getenv("GPUSOLVE_TAIL_POINTS")) h->cx.tune.tail_points = std::max(0, std::min(1 << 20, atoi(ev)));
     e = kf_prepare();
     if (e == cudaSuccess) e = kt_prepare();
     if (e == cudaSuccess) e = kx_prepare();
@@ -1123,6 +1167,7 @@ int gs_destroy(gs_handle* h)
     }
     for (auto e : h->ev_free) cudaEventDestroy(e);
     if (h->comm) gs_comm_destroy(h->comm);
+    if (h->tail) ks_tail_free(h->tail);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return GS_OK;
@@ -1499,6 +1544,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
     else if (n == "wave") h->cx.tune.wave = value != 0;
+    else if (n == "tail_points") h->cx.tune.tail_points = (int)std::max<int64_t>(0, std::min<int64_t>(1 << 20, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;
         for (auto& L : h->lev) L.ar = level_ar(L, h->opt_unit != 0, h->opt_rcp_div != 0);

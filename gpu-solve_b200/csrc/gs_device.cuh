@@ -58,23 +58,32 @@ enum { AR_POW2 = 1, AR_UNIT = 2, AR_RCP = 4 };
         }                                                                       \
     } while (0)
 
+// The point functions are __host__ __device__ only so that a CPU test can run the coarse-tail interpreter of
+// kernels_simple.cu over host arrays (tests/tail_host_check.cu); the library itself never calls them on the host.
+#define GS_HD __host__ __device__ __forceinline__
+#ifdef __CUDA_ARCH__
+#define GS_FMA(a, b, c) __fma_rn(a, b, c)
+#else
+#define GS_FMA(a, b, c) fma(a, b, c)
+#endif
+
 // s / (h*h) under the level's arithmetic flags; every branch returns the same bits
 template <int AR>
-__device__ __forceinline__ double div_hh(double s, const PointK& k)
+GS_HD double div_hh(double s, const PointK& k)
 {
     if (AR & AR_POW2) return s * k.inv_hh;
     if (AR & AR_RCP) {
         double q = s * k.inv_hh;
-        double r = __fma_rn(-k.hh, q, s);
-        q = __fma_rn(r, k.inv_hh, q);
-        r = __fma_rn(-k.hh, q, s);
-        return __fma_rn(r, k.inv_hh, q);
+        double r = GS_FMA(-k.hh, q, s);
+        q = GS_FMA(r, k.inv_hh, q);
+        r = GS_FMA(-k.hh, q, s);
+        return GS_FMA(r, k.inv_hh, q);
     }
     return s / k.hh;
 }
 
 template <int KM, int AR>
-__device__ __forceinline__ double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
+GS_HD double finish_residual(double s, double vc, double fc, double aux, const PointK& k, double& den)
 {
     s = div_hh<AR>(s, k);
     den = 0.0;
@@ -98,7 +107,7 @@ __device__ __forceinline__ double finish_residual(double s, double vc, double fc
 }
 
 template <int KM>
-__device__ __forceinline__ double jacobi_update(double vc, double r, double den, const PointK& k)
+GS_HD double jacobi_update(double vc, double r, double den, const PointK& k)
 {
     // src/cpu/CpuSolver.cpp:158 resp. :164,:171
     if (KM == KM_LINEAR) return vc + k.omega * (k.alpha * r);

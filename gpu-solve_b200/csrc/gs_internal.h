@@ -68,7 +68,10 @@ struct Tune {
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
     int zchunk2;         // planes per CTA of the two-sweep kernel
     int wave;            // 1: size z chunks so the grid fills whole waves of resident CTAs (gs_pick_zchunk_waves)
+    int tail_points;     // > 0: levels with at most this many interior points run as ONE single-CTA kernel per V-cycle (ks_tail_*); 0 = off
 };
+
+struct TailRec;  // kernels_simple.cu: the operator list of the coarse tail of a V-cycle
 
 struct LaunchCtx {
     cudaStream_t stream;
@@ -76,6 +79,7 @@ struct LaunchCtx {
     NormBuf norm;
     uint64_t* launches;   // host counter of kernels launched
     int sm_count;
+    TailRec* rec;         // non-null while the coarse tail is being recorded: ks_* append to it instead of launching
 };
 
 // ---- kernels_simple.cu: one thread per lattice point, any 7 in-range offsets ----
@@ -104,6 +108,18 @@ cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, d
 cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* dst, const double* src, int sign);
 // analytic right-hand side, src/cpu/CpuGridData.cpp:45-78 (local planes [0, nzl))
 cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f);
+
+// whole-array helpers that take part in the recording (plain cudaMemsetAsync / cudaMemcpyAsync otherwise)
+cudaError_t ks_zero(const LaunchCtx& cx, double* a, size_t count);
+cudaError_t ks_copy(const LaunchCtx& cx, double* dst, const double* src, size_t count);
+// Coarse tail: the levels below ~16^3 cost a few microseconds of launch latency per operator and nothing else.  Between
+// ks_tail_begin and ks_tail_end every ks_* call above is appended to a program instead of being launched, and ks_tail_end
+// runs the program as one kernel of one CTA (operators separated by __syncthreads, same per-point functions, hence
+// the same bits).  The program travels as a kernel parameter, so a captured graph needs no device-side copy of it.
+TailRec* ks_tail_new();
+void ks_tail_free(TailRec* r);
+void ks_tail_begin(LaunchCtx& cx, TailRec* r);
+cudaError_t ks_tail_end(LaunchCtx& cx);
 
 // ---- kernels_fast.cu: tuned sm_100a kernels for the canonical axis-aligned stencil ----
 bool kf_available();

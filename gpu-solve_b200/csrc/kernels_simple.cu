@@ -9,6 +9,8 @@
 // (cited per function, paths relative to the reference root).  Linear-mode
 // fields are therefore bit-identical to GpuSolve-cpu; modes with exp() differ by
 // CUDA-vs-glibc exp rounding only.
+#include <string.h>
+
 #include "gs_device.cuh"
 
 namespace {
@@ -26,13 +28,28 @@ struct SmoothP {
     const double* aux;
 };
 
-__device__ __forceinline__ double tap_sum(const double* __restrict__ a, i64 c, const double (&cv)[7], const i64 (&toff)[7])
+GS_HD double tap_sum(const double* __restrict__ a, i64 c, const double (&cv)[7], const i64 (&toff)[7])
 {
     // src/cpu/CpuSolver.cpp:56-60: stencilsum = 0.0; stencilsum += values[i] * v(p + o_i), i ascending
     double s = 0.0;
 #pragma unroll
     for (int i = 0; i < 7; i++) s += cv[i] * a[c + toff[i]];
     return s;
+}
+
+// The per-point bodies are functions of (x, y, local plane) so that the grid kernels below and the single-CTA tail
+// kernel at the end of this file run the very same code.
+template <int KM, bool POW2>
+GS_HD void smooth_point(const Geom& g, const PointK& k, const i64 (&toff)[7], const double* vin, double* vout,
+                                             const double* f, const double* auxp, int x, int y, int zl)
+{
+    const i64 c = gs_idx(g, x, y, zl);
+    const double vc = vin[c];
+    double s = tap_sum(vin, c, k.c, toff);
+    const double aux = (KM >= KM_NEWTON_EXP) ? auxp[c] : 0.0;
+    double den;
+    const double r = finish_residual<KM, POW2>(s, vc, f[c], aux, k, den);
+    vout[c] = jacobi_update<KM>(vc, r, den, k);
 }
 
 template <int KM, bool POW2>
@@ -42,13 +59,7 @@ __global__ void __launch_bounds__(BX* BY) smooth_simple(SmoothP p)
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + p.zb;
     if (x > p.g.nx || y > p.g.ny) return;
-    const i64 c = gs_idx(p.g, x, y, zl);
-    const double vc = p.vin[c];
-    double s = tap_sum(p.vin, c, p.k.c, p.toff);
-    const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
-    double den;
-    const double r = finish_residual<KM, POW2>(s, vc, p.f[c], aux, p.k, den);
-    p.vout[c] = jacobi_update<KM>(vc, r, den, p.k);
+    smooth_point<KM, POW2>(p.g, p.k, p.toff, p.vin, p.vout, p.f, p.aux, x, y, zl);
 }
 
 struct ResidP {
@@ -65,6 +76,20 @@ struct ResidP {
 
 // CpuSolver::compResidual, src/cpu/CpuSolver.cpp:45-83
 template <int KM, bool POW2>
+GS_HD double residual_point(const Geom& g, const PointK& k, const i64 (&toff)[7], const double* v, const double* f,
+                                                 const double* auxp, double* rout, int x, int y, int zl)
+{
+    const i64 c = gs_idx(g, x, y, zl);
+    const double vc = v[c];
+    double s = tap_sum(v, c, k.c, toff);
+    const double aux = (KM >= KM_NEWTON_EXP) ? auxp[c] : 0.0;
+    double den;
+    const double r = finish_residual<KM, POW2>(s, vc, f[c], aux, k, den);
+    if (rout) rout[c] = r;
+    return r;
+}
+
+template <int KM, bool POW2>
 __global__ void __launch_bounds__(BX* BY) residual_simple(ResidP p)
 {
     __shared__ double sh[32];
@@ -73,13 +98,7 @@ __global__ void __launch_bounds__(BX* BY) residual_simple(ResidP p)
     const int zl = blockIdx.z + p.zb;
     double sq = 0.0;
     if (x <= p.g.nx && y <= p.g.ny) {
-        const i64 c = gs_idx(p.g, x, y, zl);
-        const double vc = p.v[c];
-        double s = tap_sum(p.v, c, p.k.c, p.toff);
-        const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
-        double den;
-        const double r = finish_residual<KM, POW2>(s, vc, p.f[c], aux, p.k, den);
-        if (p.r) p.r[c] = r;
+        const double r = residual_point<KM, POW2>(p.g, p.k, p.toff, p.v, p.f, p.aux, p.r, x, y, zl);
         sq = r * r;
     }
     const int tid = threadIdx.x + threadIdx.y * BX;
@@ -97,14 +116,11 @@ struct RestrictP {
 
 // CpuSolver::restrict, src/cpu/CpuSolver.cpp:211-238: running sum over the 27
 // neighbours, x offset outermost, z offset innermost, weights 0.125*w*w*w
-__global__ void __launch_bounds__(BX* BY) restrict_simple(RestrictP p)
+GS_HD void restrict_point(const Geom& gf, const Geom& gc, const double* fine, double* coarse, double* coarse2,
+                                               int x, int y, int zc)
 {
-    const int x = blockIdx.x * BX + threadIdx.x + 1;
-    const int y = blockIdx.y * BY + threadIdx.y + 1;
-    const int zc = blockIdx.z + p.zb;  // local coarse plane
-    if (x > p.gc.nx || y > p.gc.ny) return;
-    const int zf = 2 * (zc + p.gc.z0) - p.gf.z0;  // local fine plane of the centre
-    const i64 fc = gs_idx(p.gf, 2 * x, 2 * y, zf);
+    const int zf = 2 * (zc + gc.z0) - gf.z0;  // local fine plane of the centre
+    const i64 fc = gs_idx(gf, 2 * x, 2 * y, zf);
     const double w[3] = {0.5, 1.0, 0.5};
     double acc = 0.0;
 #pragma unroll
@@ -114,11 +130,20 @@ __global__ void __launch_bounds__(BX* BY) restrict_simple(RestrictP p)
 #pragma unroll
             for (int kk = -1; kk < 2; kk++) {
                 const double fac = 0.125 * w[ii + 1] * w[jj + 1] * w[kk + 1];
-                acc += fac * p.fine[fc + ii + jj * p.gf.pitch + kk * p.gf.plane];
+                acc += fac * fine[fc + ii + jj * gf.pitch + kk * gf.plane];
             }
-    const i64 cc = gs_idx(p.gc, x, y, zc);
-    p.coarse[cc] = acc;
-    if (p.coarse2) p.coarse2[cc] = acc;
+    const i64 cc = gs_idx(gc, x, y, zc);
+    coarse[cc] = acc;
+    if (coarse2) coarse2[cc] = acc;
+}
+
+__global__ void __launch_bounds__(BX* BY) restrict_simple(RestrictP p)
+{
+    const int x = blockIdx.x * BX + threadIdx.x + 1;
+    const int y = blockIdx.y * BY + threadIdx.y + 1;
+    const int zc = blockIdx.z + p.zb;  // local coarse plane
+    if (x > p.gc.nx || y > p.gc.ny) return;
+    restrict_point(p.gf, p.gc, p.fine, p.coarse, p.coarse2, x, y, zc);
 }
 
 struct ProlongP {
@@ -134,7 +159,7 @@ struct ProlongP {
 // v += e (:131-132).  The four dependent passes of the reference (inject, x, y, z
 // averages) nest as  e = avg_z(avg_y(avg_x(C)))  with avg = 0.5*a + 0.5*b on odd
 // indices and identity on even ones; same operations, same order => same bits.
-__device__ __forceinline__ double prolong_point(const double* __restrict__ cv, const Geom& gc, int X, int Y, int Zg)
+GS_HD double prolong_point(const double* __restrict__ cv, const Geom& gc, int X, int Y, int Zg)
 {
     const int i = X >> 1, j = Y >> 1, k = (Zg >> 1) - gc.z0;
     const bool ox = X & 1, oy = Y & 1, oz = Zg & 1;
@@ -144,16 +169,22 @@ __device__ __forceinline__ double prolong_point(const double* __restrict__ cv, c
     return oz ? 0.5 * ay(b) + 0.5 * ay(b + gc.plane) : ay(b);
 }
 
+GS_HD void prolong_correct_point(const Geom& gf, const Geom& gc, const double* vin, double* vout, const double* coarse,
+                                                      double* e_out, int x, int y, int zl)
+{
+    const double e = prolong_point(coarse, gc, x, y, zl + gf.z0);
+    const i64 c = gs_idx(gf, x, y, zl);
+    if (e_out) e_out[c] = e;
+    if (vout) vout[c] = vin[c] + e;
+}
+
 __global__ void __launch_bounds__(BX* BY) prolong_correct_simple(ProlongP p)
 {
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + p.zb;
     if (x > p.gf.nx || y > p.gf.ny) return;
-    const double e = prolong_point(p.coarse, p.gc, x, y, zl + p.gf.z0);
-    const i64 c = gs_idx(p.gf, x, y, zl);
-    if (p.e_out) p.e_out[c] = e;
-    if (p.vout) p.vout[c] = p.vin[c] + e;
+    prolong_correct_point(p.gf, p.gc, p.vin, p.vout, p.coarse, p.e_out, x, y, zl);
 }
 
 struct FasP {
@@ -168,20 +199,27 @@ struct FasP {
 
 // CpuSolver::applyStencil (src/cpu/CpuSolver.cpp:182-209) on restV, then f += r (:112)
 template <bool POW2>
+GS_HD void fas_rhs_point(const Geom& g, const PointK& k, const i64 (&toff)[7], const double* restv, double* f,
+                                              double* r_out, int x, int y, int zl)
+{
+    const i64 c = gs_idx(g, x, y, zl);
+    const double vc = restv[c];
+    double s = tap_sum(restv, c, k.c, toff);
+    s = POW2 ? s * k.inv_hh : s / k.hh;
+    const double nl = (k.gamma * vc) * exp(vc);
+    s += nl;
+    if (r_out) r_out[c] = s;
+    f[c] = f[c] + s;
+}
+
+template <bool POW2>
 __global__ void __launch_bounds__(BX* BY) fas_rhs_simple(FasP p)
 {
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + p.zb;
     if (x > p.g.nx || y > p.g.ny) return;
-    const i64 c = gs_idx(p.g, x, y, zl);
-    const double vc = p.restv[c];
-    double s = tap_sum(p.restv, c, p.k.c, p.toff);
-    s = POW2 ? s * p.k.inv_hh : s / p.k.hh;
-    const double nl = (p.k.gamma * vc) * exp(vc);
-    s += nl;
-    if (p.r_out) p.r_out[c] = s;
-    p.f[c] = p.f[c] + s;
+    fas_rhs_point<POW2>(p.g, p.k, p.toff, p.restv, p.f, p.r_out, x, y, zl);
 }
 
 struct NewtonFP {
@@ -221,6 +259,13 @@ __global__ void __launch_bounds__(BX* BY) newton_F_simple(NewtonFP p)
     grid_sum_finish<BX * BY>(tot, p.nb, sh, tid);
 }
 
+GS_HD void newton_coef_point(const Geom& g, double gamma, const double* nv, double* coef, int x, int y, int zl)
+{
+    const i64 c = gs_idx(g, x, y, zl);
+    const double n = nv[c];
+    coef[c] = (gamma * (1 + n)) * exp(n);
+}
+
 __global__ void __launch_bounds__(BX* BY) newton_coef_simple(Geom g, int zb, double gamma, const double* __restrict__ nv,
                                                               double* __restrict__ coef)
 {
@@ -228,13 +273,17 @@ __global__ void __launch_bounds__(BX* BY) newton_coef_simple(Geom g, int zb, dou
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + zb;
     if (x > g.nx || y > g.ny) return;
-    const i64 c = gs_idx(g, x, y, zl);
-    const double n = nv[c];
-    coef[c] = (gamma * (1 + n)) * exp(n);
+    newton_coef_point(g, gamma, nv, coef, x, y, zl);
 }
 
 // Vector3::operator+= / -= (src/cpu/Vector3.cpp:34-54); the halo of every src
 // operand the V-cycle uses is zero, so the interior is the whole effect
+GS_HD void axpy_point(const Geom& g, double* dst, const double* src, int sign, int x, int y, int zl)
+{
+    const i64 c = gs_idx(g, x, y, zl);
+    dst[c] = sign >= 0 ? dst[c] + src[c] : dst[c] - src[c];
+}
+
 __global__ void __launch_bounds__(BX* BY) axpy_simple(Geom g, int zb, double* __restrict__ dst, const double* __restrict__ src,
                                                        int sign)
 {
@@ -242,8 +291,7 @@ __global__ void __launch_bounds__(BX* BY) axpy_simple(Geom g, int zb, double* __
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + zb;
     if (x > g.nx || y > g.ny) return;
-    const i64 c = gs_idx(g, x, y, zl);
-    dst[c] = sign >= 0 ? dst[c] + src[c] : dst[c] - src[c];
+    axpy_point(g, dst, src, sign, x, y, zl);
 }
 
 // src/cpu/CpuGridData.cpp:7-12
@@ -281,6 +329,114 @@ __global__ void __launch_bounds__(BX* BY) init_rhs_simple(Geom g, int mode, doub
     }
 }
 
+
+// ---------------------------------------------------------------------------------
+// coarse tail: a recorded list of the operators above, run by ONE CTA (gs_internal.h ks_tail_*)
+// ---------------------------------------------------------------------------------
+enum { T_SMOOTH, T_RESID, T_RESTRICT, T_PROLONG, T_FAS, T_COEF, T_AXPY, T_ZERO, T_COPY };
+constexpr int TAIL_THREADS = 1024, TAIL_MAX_OPS = 96, TAIL_MAX_LEV = 12;
+
+struct TailLev {
+    Geom g;
+    PointK k;
+    i64 toff[7];
+};
+
+struct TailOp {
+    int type, pow2;
+    int la, lb;   // level-table entries: the level (fine level of a transfer), the coarse level of a transfer
+    int zb, nz;   // first local plane and number of planes of the points to visit
+    int sign, pad;
+    const double *a, *b, *c;  // inputs, in the order of the ks_* signature
+    double *o, *o2;           // outputs
+    double gamma;
+    i64 count;                // T_ZERO / T_COPY: doubles
+};
+
+struct TailProg {
+    int nops, nlev;
+    TailLev lev[TAIL_MAX_LEV];
+    TailOp op[TAIL_MAX_OPS];
+};
+static_assert(sizeof(TailProg) < 30000, "the program is passed as a kernel parameter (32764-byte limit)");
+
+// visit the nx*ny*nz points of planes [zb, zb+nz), x fastest, nthr at a time
+template <typename F>
+GS_HD void tail_points(int nx, int ny, int nz, int zb, int tid, int nthr, F body)
+{
+    const int n = nx * ny * nz;
+    for (int i = tid; i < n; i += nthr) {
+        const int x = i % nx, t = i / nx;
+        body(x + 1, t % ny + 1, t / ny + zb);
+    }
+}
+
+// thread `tid` of `nthr`: its share of one recorded operator.  KM is the same for every smoother / residual operator of
+// a cycle.  Loads are plain ld.global (no __ldg): the arrays are rewritten inside the kernel, by the same CTA.
+template <int KM>
+GS_HD void tail_do_op(const TailProg& P, const TailOp& op, int tid, int nthr)
+{
+    const TailLev& A = P.lev[op.la];
+    const TailLev& B = P.lev[op.lb];
+    switch (op.type) {
+    case T_SMOOTH:
+        if (op.pow2)
+            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                        [&](int x, int y, int z) { smooth_point<KM, true>(A.g, A.k, A.toff, op.a, op.o, op.b, op.c, x, y, z); });
+        else
+            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                        [&](int x, int y, int z) { smooth_point<KM, false>(A.g, A.k, A.toff, op.a, op.o, op.b, op.c, x, y, z); });
+        break;
+    case T_RESID:
+        if (op.pow2)
+            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                        [&](int x, int y, int z) { residual_point<KM, true>(A.g, A.k, A.toff, op.a, op.b, op.c, op.o, x, y, z); });
+        else
+            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                        [&](int x, int y, int z) { residual_point<KM, false>(A.g, A.k, A.toff, op.a, op.b, op.c, op.o, x, y, z); });
+        break;
+    case T_RESTRICT:
+        tail_points(B.g.nx, B.g.ny, op.nz, op.zb, tid, nthr,
+                    [&](int x, int y, int z) { restrict_point(A.g, B.g, op.a, op.o, op.o2, x, y, z); });
+        break;
+    case T_PROLONG:
+        tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                    [&](int x, int y, int z) { prolong_correct_point(A.g, B.g, op.a, op.o, op.b, op.o2, x, y, z); });
+        break;
+    case T_FAS:
+        if (op.pow2)
+            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                        [&](int x, int y, int z) { fas_rhs_point<true>(A.g, A.k, A.toff, op.a, op.o, op.o2, x, y, z); });
+        else
+            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                        [&](int x, int y, int z) { fas_rhs_point<false>(A.g, A.k, A.toff, op.a, op.o, op.o2, x, y, z); });
+        break;
+    case T_COEF:
+        tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
+                    [&](int x, int y, int z) { newton_coef_point(A.g, op.gamma, op.a, op.o, x, y, z); });
+        break;
+    case T_AXPY:
+        tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr, [&](int x, int y, int z) { axpy_point(A.g, op.o, op.a, op.sign, x, y, z); });
+        break;
+    case T_ZERO:
+        for (i64 j = tid; j < op.count; j += nthr) op.o[j] = 0.0;
+        break;
+    case T_COPY:
+        for (i64 j = tid; j < op.count; j += nthr) op.o[j] = op.a[j];
+        break;
+    }
+}
+
+// one CTA runs the whole program; __syncthreads orders one operator after the other
+template <int KM>
+__global__ void __launch_bounds__(TAIL_THREADS, 1) tail_kernel(const __grid_constant__ TailProg P)
+{
+    for (int i = 0; i < P.nops; i++) {
+        tail_do_op<KM>(P, P.op[i], threadIdx.x, TAIL_THREADS);
+        __syncthreads();
+    }
+}
+
 inline dim3 grid_for(int nx, int ny, int nz) { return dim3((nx + BX - 1) / BX, (ny + BY - 1) / BY, nz); }
 
 inline void fill_toff(const Geom& g, const StencilOff& so, i64 (&toff)[7])
@@ -295,6 +451,130 @@ inline cudaError_t done(const LaunchCtx& cx)
 }
 
 }  // namespace
+
+// ---- coarse-tail recorder -----------------------------------------------------------
+struct TailRec {
+    TailProg prog;
+    int km;
+    bool overflow;  // more distinct levels than the table holds: the caller must not have started this tail
+    // how a finished program is executed: the CUDA launch below.  tests/tail_host_check.cu substitutes an interpreter
+    // over host arrays to check the recorder and tail_do_op without a GPU.
+    cudaError_t (*exec)(const LaunchCtx& cx, const TailProg& P, int km);
+};
+
+namespace {
+
+int tail_level(TailRec* r, const Geom& g, const PointK* k, const StencilOff* so)
+{
+    TailLev e;
+    memset(&e, 0, sizeof e);
+    e.g = g;
+    if (k) e.k = *k;
+    if (so) fill_toff(g, *so, e.toff);
+    TailProg& P = r->prog;
+    for (int i = 0; i < P.nlev; i++) {
+        // a transfer operator only knows the geometry: it may share the entry a smoother made for the level
+        if (memcmp(&P.lev[i].g, &g, sizeof g) != 0) continue;
+        if (!k) return i;
+        if (memcmp(&P.lev[i].k, &e.k, sizeof e.k) == 0 && memcmp(P.lev[i].toff, e.toff, sizeof e.toff) == 0) return i;
+    }
+    if (P.nlev == TAIL_MAX_LEV) {
+        r->overflow = true;
+        return 0;
+    }
+    P.lev[P.nlev] = e;
+    return P.nlev++;
+}
+
+cudaError_t tail_exec_cuda(const LaunchCtx& cx, const TailProg& P, int km)
+{
+    switch (km) {
+    case KM_LINEAR: tail_kernel<KM_LINEAR><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
+    case KM_NONLINEAR: tail_kernel<KM_NONLINEAR><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
+    case KM_NEWTON_EXP: tail_kernel<KM_NEWTON_EXP><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
+    default: tail_kernel<KM_NEWTON_COEF><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
+    }
+    return done(cx);
+}
+
+cudaError_t tail_launch(const LaunchCtx& cx, TailRec* r)
+{
+    TailProg& P = r->prog;
+    if (P.nops == 0) return cudaSuccess;
+    if (r->overflow) return cudaErrorInvalidValue;
+    cudaError_t e = r->exec(cx, P, r->km);
+    P.nops = 0;  // the level table stays: the next program of the same tail uses the same levels
+    return e;
+}
+
+// append an operator; a full program is launched and a new one started (same semantics, one more kernel)
+cudaError_t tail_push(const LaunchCtx& cx, const TailOp& op)
+{
+    TailRec* r = cx.rec;
+    if (r->prog.nops == TAIL_MAX_OPS) {
+        cudaError_t e = tail_launch(cx, r);
+        if (e != cudaSuccess) return e;
+    }
+    r->prog.op[r->prog.nops++] = op;
+    return r->overflow ? cudaErrorInvalidValue : cudaSuccess;
+}
+
+TailOp tail_op(int type)
+{
+    TailOp op;
+    memset(&op, 0, sizeof op);
+    op.type = type;
+    return op;
+}
+
+}  // namespace
+
+TailRec* ks_tail_new()
+{
+    TailRec* r = new TailRec;
+    memset(&r->prog, 0, sizeof r->prog);
+    r->km = KM_LINEAR;
+    r->overflow = false;
+    r->exec = tail_exec_cuda;
+    return r;
+}
+
+void ks_tail_free(TailRec* r) { delete r; }
+
+void ks_tail_begin(LaunchCtx& cx, TailRec* r)
+{
+    r->prog.nops = 0;
+    r->prog.nlev = 0;
+    r->km = KM_LINEAR;
+    r->overflow = false;
+    cx.rec = r;
+}
+
+cudaError_t ks_tail_end(LaunchCtx& cx)
+{
+    TailRec* r = cx.rec;
+    cx.rec = nullptr;
+    return r ? tail_launch(cx, r) : cudaSuccess;
+}
+
+cudaError_t ks_zero(const LaunchCtx& cx, double* a, size_t count)
+{
+    if (!cx.rec) return cudaMemsetAsync(a, 0, count * sizeof(double), cx.stream);
+    TailOp op = tail_op(T_ZERO);
+    op.o = a;
+    op.count = (i64)count;
+    return tail_push(cx, op);
+}
+
+cudaError_t ks_copy(const LaunchCtx& cx, double* dst, const double* src, size_t count)
+{
+    if (!cx.rec) return cudaMemcpyAsync(dst, src, count * sizeof(double), cudaMemcpyDeviceToDevice, cx.stream);
+    TailOp op = tail_op(T_COPY);
+    op.o = dst;
+    op.a = src;
+    op.count = (i64)count;
+    return tail_push(cx, op);
+}
 
 #define KM_DISPATCH(KERNEL, km, pow2, ...)                                                          \
     do {                                                                                            \
@@ -319,6 +599,19 @@ cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int
                       const StencilOff& so, const double* vin, double* vout, const double* f, const double* aux)
 {
     if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaSuccess;
+    if (cx.rec) {
+        TailOp op = tail_op(T_SMOOTH);
+        cx.rec->km = km;
+        op.pow2 = pow2;
+        op.la = tail_level(cx.rec, g, &k, &so);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = vin;
+        op.b = f;
+        op.c = aux;
+        op.o = vout;
+        return tail_push(cx, op);
+    }
     SmoothP p{g, k, {}, zb, vin, vout, f, aux};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -330,6 +623,19 @@ cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
                         const StencilOff& so, const double* v, const double* f, const double* aux, double* r)
 {
     if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaErrorInvalidValue;
+    if (cx.rec) {  // inside the tail only the stored residual matters (its norm is never read)
+        TailOp op = tail_op(T_RESID);
+        cx.rec->km = km;
+        op.pow2 = pow2;
+        op.la = tail_level(cx.rec, g, &k, &so);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = v;
+        op.b = f;
+        op.c = aux;
+        op.o = r;
+        return tail_push(cx, op);
+    }
     ResidP p{g, k, {}, zb, v, f, aux, r, cx.norm};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -342,6 +648,17 @@ cudaError_t ks_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int
                         double* coarse, double* coarse2)
 {
     if (ze <= zb || gc.nx <= 0 || gc.ny <= 0) return cudaSuccess;
+    if (cx.rec) {
+        TailOp op = tail_op(T_RESTRICT);
+        op.la = tail_level(cx.rec, gf, nullptr, nullptr);
+        op.lb = tail_level(cx.rec, gc, nullptr, nullptr);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = fine;
+        op.o = coarse;
+        op.o2 = coarse2;
+        return tail_push(cx, op);
+    }
     RestrictP p{gf, gc, zb, fine, coarse, coarse2};
     restrict_simple<<<grid_for(gc.nx, gc.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
     return done(cx);
@@ -351,6 +668,19 @@ cudaError_t ks_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
                                double* vout, const double* coarse, double* e_out)
 {
     if (ze <= zb) return cudaSuccess;
+    if (cx.rec) {
+        if (gf.nx <= 0 || gf.ny <= 0) return cudaSuccess;
+        TailOp op = tail_op(T_PROLONG);
+        op.la = tail_level(cx.rec, gf, nullptr, nullptr);
+        op.lb = tail_level(cx.rec, gc, nullptr, nullptr);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = vin;
+        op.b = coarse;
+        op.o = vout;
+        op.o2 = e_out;
+        return tail_push(cx, op);
+    }
     ProlongP p{gf, gc, zb, vin, vout, coarse, e_out};
     prolong_correct_simple<<<grid_for(gf.nx, gf.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
     return done(cx);
@@ -360,6 +690,17 @@ cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, in
                        const StencilOff& so, const double* restv, double* f, double* r_out)
 {
     if (ze <= zb) return cudaSuccess;
+    if (cx.rec) {
+        TailOp op = tail_op(T_FAS);
+        op.pow2 = pow2;
+        op.la = tail_level(cx.rec, g, &k, &so);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = restv;
+        op.o = f;
+        op.o2 = r_out;
+        return tail_push(cx, op);
+    }
     FasP p{g, k, {}, zb, restv, f, r_out};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -371,7 +712,7 @@ cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, in
 cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
                         const StencilOff& so, const double* nv, const double* newtonF, double* f)
 {
-    if (ze <= zb) return cudaErrorInvalidValue;
+    if (ze <= zb || cx.rec) return cudaErrorInvalidValue;  // level 0 with its norm: never part of a tail
     NewtonFP p{g, k, {}, zb, nv, newtonF, f, cx.norm};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -384,6 +725,16 @@ cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, i
 cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, double gamma, const double* nv, double* coef)
 {
     if (ze <= zb) return cudaSuccess;
+    if (cx.rec) {
+        TailOp op = tail_op(T_COEF);
+        op.la = tail_level(cx.rec, g, nullptr, nullptr);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = nv;
+        op.o = coef;
+        op.gamma = gamma;
+        return tail_push(cx, op);
+    }
     newton_coef_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, gamma, nv, coef);
     return done(cx);
 }
@@ -391,12 +742,23 @@ cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, d
 cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* dst, const double* src, int sign)
 {
     if (ze <= zb) return cudaSuccess;
+    if (cx.rec) {
+        TailOp op = tail_op(T_AXPY);
+        op.la = tail_level(cx.rec, g, nullptr, nullptr);
+        op.zb = zb;
+        op.nz = ze - zb;
+        op.a = src;
+        op.o = dst;
+        op.sign = sign;
+        return tail_push(cx, op);
+    }
     axpy_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, dst, src, sign);
     return done(cx);
 }
 
 cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f)
 {
+    if (cx.rec) return cudaErrorInvalidValue;
     init_rhs_simple<<<grid_for(g.X, g.Y, g.nzl), dim3(BX, BY), 0, cx.stream>>>(g, mode, h, gamma, f);
     return done(cx);
 }
