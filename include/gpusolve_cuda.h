@@ -194,7 +194,12 @@ uint64_t gs_launch_count(const gs_handle* h);
  *          "fuse2" = 0 one Jacobi sweep per pass, 1..3 two sweeps per pass (tile variant,
  *          kernels_fused.cu; default 1), "fuse2_min_n", "zchunk2" its knobs;
  *          "fuse_norm" = 0/1 produce the next pre-smoothing sweep(s) together with the
- *          V-cycle's final residual norm (default 1); also GPUSOLVE_* environment */
+ *          V-cycle's final residual norm (default 1);
+ *          "unit_taps", "rcp_div", "wave", "vzero" = 0/1 same bits, slower (A/B switches, default 1);
+ *          "timers" = 0/1 partial-timer lines in the reference Timer's format after a solve;
+ *          "tail_points" = N > 0: levels of at most N interior points run as one single-CTA
+ *          kernel per V-cycle (kernels_simple.cu ks_tail_*; default 0 = off);
+ *          also GPUSOLVE_* environment */
 int  gs_set_option(gs_handle* h, const char* name, int64_t value);
 /* the CUDA stream all work of this handle is issued on (a cudaStream_t) */
 void* gs_stream(gs_handle* h);
