@@ -456,7 +456,8 @@ inline cudaError_t done(const LaunchCtx& cx)
 struct TailRec {
     TailProg prog;
     int km;
-    bool overflow;  // more distinct levels than the table holds: the caller must not have started this tail
+    bool overflow;  // more distinct levels than the table holds (cannot happen: one entry per level, 12 levels at most)
+    bool has_k[TAIL_MAX_LEV];  // entry carries the point constants (made or completed by a smoother-type operator)
     // how a finished program is executed: the CUDA launch below.  tests/tail_host_check.cu substitutes an interpreter
     // over host arrays to check the recorder and tail_do_op without a GPU.
     cudaError_t (*exec)(const LaunchCtx& cx, const TailProg& P, int km);
@@ -473,9 +474,13 @@ int tail_level(TailRec* r, const Geom& g, const PointK* k, const StencilOff* so)
     if (so) fill_toff(g, *so, e.toff);
     TailProg& P = r->prog;
     for (int i = 0; i < P.nlev; i++) {
-        // a transfer operator only knows the geometry: it may share the entry a smoother made for the level
         if (memcmp(&P.lev[i].g, &g, sizeof g) != 0) continue;
-        if (!k) return i;
+        if (!k) return i;  // a transfer operator only needs the geometry
+        if (!r->has_k[i]) {  // entry made by a transfer operator: complete it (nothing recorded so far reads its constants)
+            P.lev[i] = e;
+            r->has_k[i] = true;
+            return i;
+        }
         if (memcmp(&P.lev[i].k, &e.k, sizeof e.k) == 0 && memcmp(P.lev[i].toff, e.toff, sizeof e.toff) == 0) return i;
     }
     if (P.nlev == TAIL_MAX_LEV) {
@@ -483,6 +488,7 @@ int tail_level(TailRec* r, const Geom& g, const PointK* k, const StencilOff* so)
         return 0;
     }
     P.lev[P.nlev] = e;
+    r->has_k[P.nlev] = k != nullptr;
     return P.nlev++;
 }
 

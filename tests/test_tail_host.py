@@ -61,6 +61,7 @@ def run_case(harness, oracle_mod, n, mode, pre, post, tail, cycles=2, km_coef=0,
     (15, 0, 2, 2, 1),
     (15, 0, 2, 2, -1),           # no tail: every operator its own program
     (31, 0, 2, 2, 1),
+    (63, 0, 2, 2, 0),            # six levels in one level table
     ((9, 12, 17), 0, 1, 3, 0),   # ragged, h*h not a power of two
     (18, 0, 2, 1, 0),            # even extents, odd sweep count (out-of-place correction, parity copy)
     ((3, 5, 4), 0, 2, 2, 0),
