@@ -167,3 +167,21 @@ def test_zchunk_plan_fills_whole_waves(gs, tiles, planes, occ, overhead, lo, hi,
     if (tiles, planes) == (387, 511):
         ctas = tiles * -(-planes // chunk)
         assert ctas / (sm * occ) > 0.97 * -(-ctas // (sm * occ))
+
+
+def test_product_sources_never_touch_the_oracle_or_a_host_compute_path():
+    """the oracle is test infrastructure: nothing under the package (library sources, driver, ctypes view) or in the
+    public header may include, import, link or name it; and the library exports no host-side compute entry (the
+    __host__ __device__ point functions of kernels_simple.cu are only ever called on the host by tests/tail_host_check.cu)"""
+    import re
+    pkg = os.path.join(ROOT, "gpu-solve_b200")
+    files = [os.path.join(ROOT, "include", "gpusolve_cuda.h"), os.path.join(pkg, "__init__.py"), os.path.join(pkg, "Makefile")]
+    files += [os.path.join(pkg, "csrc", f) for f in os.listdir(os.path.join(pkg, "csrc"))]
+    pat = re.compile(r"oracle|gs_oracle|gso_|_ref/", re.I)
+    for f in files:
+        with open(f) as fh:
+            for i, line in enumerate(fh, 1):
+                assert not pat.search(line), f"{f}:{i} mentions the oracle: {line.strip()}"
+    # host code of the library that loops over lattice points would be a CPU path: the only per-point code is device code
+    api = open(os.path.join(pkg, "csrc", "gs_api.cu")).read()
+    assert "tail_do_op" not in api and "_point(" not in api
