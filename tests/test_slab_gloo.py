@@ -55,3 +55,26 @@ def test_slab_sweeps_over_gloo_equal_whole_grid_oracle(gs, oracle_mod, tmp_path,
     assert np.array_equal(got["v"], o.get(0, V)), "slab result differs from the whole-grid reference"
     assert abs(np.sqrt(float(got["sumsq"])) - norm4) <= 1e-12 * norm4
     o.close()
+
+
+@pytest.mark.parametrize("n,world", [(63, 2), (63, 3), (63, 4)])
+def test_slab_vcycles_over_gloo_equal_whole_grid_oracle(oracle_mod, tmp_path, monkeypatch, n, world):
+    """whole V(2,2) cycles on z-slabs with the partition the library computes: partitioned levels with lazy two-plane
+    ghosts, coarse-aligned restriction across the slab boundary, the first replicated level gathered, prolongation from
+    a one-plane coarse ghost — fields equal the whole-grid oracle bit for bit after every cycle count tried"""
+    import torch.multiprocessing as mp
+    monkeypatch.setenv("GPUSOLVE_SLAB_MIN_POINTS", "1000")
+    out = str(tmp_path / "mg.npz")
+    cycles = 2
+    mp.spawn(slab_model.vcycle_worker, args=(world, _free_port(), n, 41, cycles, out), nprocs=world, join=True)
+    got = np.load(out)
+    assert int(got["rep"]) >= 2, "the test wants at least two partitioned levels"
+    o = oracle_mod.Oracle(oracle_mod.make_params(n, mode=0, pre=2, post=2, maxiter=1, tol=1e-30), "port")
+    shape = o.shape(0)
+    o.set(0, V, seeded_field(shape, 41))
+    o.set(0, F, seeded_field(shape, 42, scale=1.0))
+    norms = [o.vcycle() for _ in range(cycles)]
+    assert np.array_equal(got["v"], o.get(0, V)), "slab V-cycle differs from the whole-grid reference"
+    for s, want in zip(got["sums"], norms):
+        assert abs(np.sqrt(s) - want) <= 1e-12 * want
+    o.close()
