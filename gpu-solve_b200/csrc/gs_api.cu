@@ -106,6 +106,9 @@ struct gs_handle {
     double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
     size_t stage_count;
     TailRec* tail;        // recorder of the coarse tail (cx.tune.tail_points > 0), made on first use
+    int opt_overlap;      // slabs: ghost refresh on a second stream, overlapped with the interior of the operator that needs it
+    cudaStream_t stream2;
+    cudaEvent_t ev_fork, ev_join;
 };
 
 namespace {
@@ -311,6 +314,34 @@ int need_v_halo(gs_handle* h, int level, int depth)
     return GS_OK;
 }
 
+// Overlapped ghost refresh (opt_overlap, slabs): the exchange of the two ghost planes of v runs on a second stream
+// while the operator runs on the planes that read no ghost; after the join it runs on a band at each side that has a
+// neighbour.  Same kernels and per-point arithmetic, only the plane ranges of the launches differ, so the fields stay
+// bit-identical.  `band` = owned fine planes the operator wants per boundary launch.
+int halo_begin(gs_handle* h, int level, int band, bool* started)
+{
+    *started = false;
+    Level& L = h->lev[level];
+    if (!h->opt_overlap || !partitioned(h, level) || L.gv >= 2 || !h->stream2) return GS_OK;
+    const int sides = (L.zlo > 0 ? 1 : 0) + (L.zhi < L.g.Zg ? 1 : 0);
+    if (L.ie - L.ib < (sides + 1) * band) return GS_OK;  // thin slab: plain exchange, one launch
+    CU(cudaEventRecord(h->ev_fork, h->stream));
+    CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+    const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;
+    if (gs_comm_halo(h->comm, L.v, L.g.plane, lo, hi, 2, L.zlo, L.zhi, L.g.Zg, h->stream2) != 0)
+        return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
+    CU(cudaEventRecord(h->ev_join, h->stream2));
+    *started = true;
+    return GS_OK;
+}
+
+int halo_end(gs_handle* h, int level)
+{
+    CU(cudaStreamWaitEvent(h->stream, h->ev_join, 0));
+    h->lev[level].gv = 2;
+    return GS_OK;
+}
+
 // ---- operators ------------------------------------------------------------------
 int ensure_coef(gs_handle* h, int level)
 {
@@ -366,6 +397,28 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     }
     while (iters > 0) {
         bool handled = false;
+        if (iters >= 2 && tuned && h->cx.tune.fuse2) {
+            constexpr int BAND = 16;  // kx_smooth2 takes no shorter range
+            bool started = false;
+            GS(halo_begin(h, level, BAND, &started));
+            if (started) {
+                const int lo_b = L.zlo > 0 ? BAND : 0, hi_b = L.zhi < L.g.Zg ? BAND : 0;
+                CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib + lo_b, L.ie - hi_b, L.k, L.v, L.vtmp, L.f, aux, false, false, &handled));
+                GS(halo_end(h, level));
+                if (handled) {
+                    bool hb = true;
+                    if (lo_b) CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ib + lo_b, L.k, L.v, L.vtmp, L.f, aux, false, false, &hb));
+                    if (hi_b && hb) CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ie - hi_b, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, false, &hb));
+                    if (!hb) return fail(GS_ECUDA, "boundary band of the overlapped smoother was not launched (level %d)", level);
+                    iters -= 2;
+                    h->lvl_sweeps[level] += 2;
+                    std::swap(L.v, L.vtmp);
+                    L.gv = 0;
+                    continue;
+                }
+                // the level is too small for the two-sweep kernel: the ghosts are current now, take the plain path
+            }
+        }
         GS(need_v_halo(h, level, (iters >= 2 && tuned && h->cx.tune.fuse2) ? 2 : 1));
         if (iters >= 2 && tuned) {
             // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
@@ -492,13 +545,34 @@ int do_restrict_residual(gs_handle* h, int level)
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_RESTRICT, level);
     int zb = L.ib, ze = L.ie;
+    int km = smoother_km(h);
+    if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     if (partitioned(h, level)) {
+        if (h->opt_kernels && h->canonical && !h->cx.rec) {
+            // overlapped: the coarse planes away from the slab boundaries first, a band of four at each side after the join
+            constexpr int CB = 4;  // kt_resid_restrict takes no shorter range
+            int czb, cze;
+            coarse_range(h, level, &czb, &cze);
+            const int lo_b = L.zlo > 0 ? CB : 0, hi_b = L.zhi < L.g.Zg ? CB : 0;
+            bool started = false;
+            if (cze - czb >= lo_b + hi_b + CB) GS(halo_begin(h, level, 2 * CB, &started));
+            if (started) {
+                bool handled = false;
+                CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb + lo_b, cze - hi_b, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
+                GS(halo_end(h, level));
+                if (handled) {
+                    bool hb = true;
+                    if (lo_b) CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, czb + lo_b, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &hb));
+                    if (hi_b && hb) CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, cze - hi_b, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &hb));
+                    if (!hb) return fail(GS_ECUDA, "boundary band of the overlapped residual+restriction was not launched (level %d)", level);
+                    return finish_coarse(h, level, C.f);
+                }
+            }
+        }
         // the lowest owned coarse plane needs r one fine plane below the slab, which needs v two below
         GS(need_v_halo(h, level, 2));
         if (L.zlo > 0) zb = L.ib - 1;
     }
-    int km = smoother_km(h);
-    if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     if (h->opt_kernels && h->canonical && !h->cx.rec) {
         // fused: the residual never goes to memory (kernels_transfer.cu)
         int czb, cze;
@@ -642,6 +716,7 @@ uint64_t parity_key(const gs_handle* h)
     key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
     key ^= (uint64_t)(h->opt_vzero & 1) << 8;
     key ^= (uint64_t)(tail_first_level(h) + 1) * 0xD6E8FEB86659FD93ull;
+    key ^= (uint64_t)(h->opt_overlap & 1) << 7;
     key |= (uint64_t)(h->p.pre & 0xff) << 44;
     key |= (uint64_t)(h->p.post & 0xff) << 52;
     // slabs: which ghost planes are current decides which exchanges the captured cycle contains
@@ -943,6 +1018,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->stage_count = 0;
     h->tail = nullptr;
     h->cx.rec = nullptr;
+    h->opt_overlap = 0;  // prepared, off until it has been through a multi-GPU run
+    h->stream2 = nullptr;
+    h->ev_fork = h->ev_join = nullptr;
+    if (const char* e = getenv("GPUSOLVE_OVERLAP")) h->opt_overlap = atoi(e) != 0;
     memset(h->op_ms, 0, sizeof h->op_ms);
     memset(h->op_launches, 0, sizeof h->op_launches);
     for (int i = 0; i < 7; i++) {
@@ -1065,6 +1144,13 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     }
 
     if (world > 1) {
+        e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+        if (e != cudaSuccess) {
+            gs_destroy(h);
+            return fail(GS_ECUDA, "second stream setup failed: %s", cudaGetErrorString(e));
+        }
         std::vector<int> bounds;
         for (int l = 0; l < nlev; l++)
             for (int r = 0; r <= world; r++) bounds.push_back(part.b[l][r]);
@@ -1168,6 +1254,9 @@ int gs_destroy(gs_handle* h)
     for (auto e : h->ev_free) cudaEventDestroy(e);
     if (h->comm) gs_comm_destroy(h->comm);
     if (h->tail) ks_tail_free(h->tail);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return GS_OK;
@@ -1544,6 +1633,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
     else if (n == "wave") h->cx.tune.wave = value != 0;
+    else if (n == "overlap") h->opt_overlap = value != 0;
     else if (n == "tail_points") h->cx.tune.tail_points = (int)std::max<int64_t>(0, std::min<int64_t>(1 << 20, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;

@@ -199,6 +199,8 @@ uint64_t gs_launch_count(const gs_handle* h);
  *          "timers" = 0/1 partial-timer lines in the reference Timer's format after a solve;
  *          "tail_points" = N > 0: levels of at most N interior points run as one single-CTA
  *          kernel per V-cycle (kernels_simple.cu ks_tail_*; default 0 = off);
+ *          "overlap" = 0/1 slabs: refresh the ghost planes on a second stream while the operator that
+ *          needs them runs on the planes that read no ghost (default 0);
  *          also GPUSOLVE_* environment */
 int  gs_set_option(gs_handle* h, const char* name, int64_t value);
 /* the CUDA stream all work of this handle is issued on (a cudaStream_t) */

@@ -16,5 +16,14 @@ if [ -z "$skip" ]; then
 fi
 timeout 150 $TR bench.py --gpus $N --steps 20 --warmup 5 --no-e2e 2> $out/${tag}_bench_weak.err | grep '"metric"' > $out/${tag}_bench_weak_${N}gpu.json
 timeout 200 $TR bench.py --gpus $N --steps 10 --warmup 3 --grid 1023 --no-e2e 2> $out/${tag}_bench_1023.err | grep '"metric"' > $out/${tag}_bench_1023_${N}gpu.json
+# prepared variant (default off): ghost refresh overlapped with the interior launches; parity first, then the same bench lines
+GPUSOLVE_OVERLAP=1 timeout 120 $TR tools/check_multigpu.py --grid 511 --mode 0 --cycles 2 2>&1 | grep -E "world|Error|error" > $out/${tag}_overlap_check511.log
+echo "exit ${PIPESTATUS[0]}" >> $out/${tag}_overlap_check511.log
+for mode in 1 2; do
+  GPUSOLVE_OVERLAP=1 timeout 120 $TR tools/check_multigpu.py --grid 255 --mode $mode --cycles 2 2>&1 | grep -E "world|Error|error" > $out/${tag}_overlap_check255_mode$mode.log
+  echo "exit ${PIPESTATUS[0]}" >> $out/${tag}_overlap_check255_mode$mode.log
+done
+GPUSOLVE_OVERLAP=1 timeout 150 $TR bench.py --gpus $N --steps 20 --warmup 5 --no-e2e 2> $out/${tag}_overlap_bench_weak.err | grep '"metric"' > $out/${tag}_overlap_bench_weak_${N}gpu.json
+GPUSOLVE_OVERLAP=1 timeout 200 $TR bench.py --gpus $N --steps 10 --warmup 3 --grid 1023 --no-e2e 2> $out/${tag}_overlap_bench_1023.err | grep '"metric"' > $out/${tag}_overlap_bench_1023_${N}gpu.json
 NCCL_DEBUG=INFO timeout 60 $TR tools/check_multigpu.py --grid 255 --mode 0 --cycles 1 2>&1 | grep -E "NVLS|P2P|via" | head -20 > $out/${tag}_nccl_transport.txt
 echo done
