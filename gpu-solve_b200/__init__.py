@@ -64,7 +64,8 @@ def make_params(n, mode=0, pre=2, post=2, maxiter=10, tol=1e-5, omega=0.8, gamma
 
 def build(verbose=False):
     """compile the CUDA backend in-tree for sm_100a (nvcc cross-compiles without a GPU)"""
-    r = subprocess.run(["make", "-C", HERE], capture_output=True, text=True)
+    jobs = str(max(1, min(8, os.cpu_count() or 1)))  # the five translation units compile independently
+    r = subprocess.run(["make", "-C", HERE, "-j", jobs], capture_output=True, text=True)
     if verbose or r.returncode != 0:
         print(r.stdout[-4000:], r.stderr[-4000:])
     if r.returncode != 0:
