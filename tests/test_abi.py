@@ -185,3 +185,50 @@ def test_product_sources_never_touch_the_oracle_or_a_host_compute_path():
     # host code of the library that loops over lattice points would be a CPU path: the only per-point code is device code
     api = open(os.path.join(pkg, "csrc", "gs_api.cu")).read()
     assert "tail_do_op" not in api and "_point(" not in api
+
+
+def _check_partition(gs, n, world):
+    import math
+    p = gs.make_params(n)
+    dims = [n] * 3 if isinstance(n, int) else list(n)
+    nlev = int(math.floor(math.log(min(dims)) / math.log(2.0))) + 1
+    _, _, rep = gs.partition(p, world, 0, 0)
+    assert 0 <= rep <= max(nlev - 2, 0)
+    nz = dims[2]
+    for level in range(nlev):
+        Z = nz + 2
+        prev = 0
+        for r in range(world):
+            zb, ze, rep2 = gs.partition(p, world, r, level)
+            assert rep2 == rep
+            if level >= rep:
+                assert (zb, ze) == (0, Z)
+                continue
+            # every rank holds at least the four planes asked for, the last one at least two (one interior plane and
+            # the halo plane: still exchangeable two planes deep, tests/test_slab_gloo.py runs that case)
+            assert zb == prev and ze - zb >= (4 if r < world - 1 else 2), f"n={n} world={world} level={level} rank={r}: [{zb},{ze})"
+            prev = ze
+            if r < world - 1 and level + 1 < rep:
+                # coarse aligned wherever the coarse level is partitioned too; the deepest partitioned level may end a slab
+                # on an odd plane (its coarse level is held whole, gs_api.cu coarse_range rounds: tests/test_slab_gloo.py n=69)
+                _, ce, _ = gs.partition(p, world, r, level + 1)
+                assert ze == 2 * ce
+        if level < rep:
+            assert prev == Z
+        nz //= 2
+
+
+def test_partition_of_the_bench_grids(gs):
+    """the grids bench.py runs at N = 2, 4, 8 (weak) and the strong-scaling 1023^3"""
+    for world, n in ((2, (511, 511, 1023)), (4, (511, 1023, 1023)), (8, 1023), (2, 1023), (4, 1023), (8, (511, 511, 4000))):
+        _check_partition(gs, n, world)
+        _, _, rep = gs.partition(gs.make_params(n), world, 0, 0)
+        assert rep >= 1, f"{n} on {world} ranks must be partitioned"
+
+
+def test_partition_invariants_on_random_grids(gs):
+    import random
+    rnd = random.Random(7)
+    for _ in range(300):
+        n = tuple(rnd.randint(1, 1200) for _ in range(3))
+        _check_partition(gs, n, rnd.randint(2, 8))

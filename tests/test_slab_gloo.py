@@ -57,7 +57,9 @@ def test_slab_sweeps_over_gloo_equal_whole_grid_oracle(gs, oracle_mod, tmp_path,
     o.close()
 
 
-@pytest.mark.parametrize("n,world", [(63, 2), (63, 3), (63, 4)])
+@pytest.mark.parametrize("n,world", [(69, 2), (63, 3), (63, 4), (25, 4)])
+# 69: even-sized levels and an odd slab boundary on the deepest partitioned level; 25 on 4 ranks: the last rank holds one
+# interior plane plus the halo plane of the deepest partitioned level
 def test_slab_vcycles_over_gloo_equal_whole_grid_oracle(oracle_mod, tmp_path, monkeypatch, n, world):
     """whole V(2,2) cycles on z-slabs with the partition the library computes: partitioned levels with lazy two-plane
     ghosts, coarse-aligned restriction across the slab boundary, the first replicated level gathered, prolongation from
