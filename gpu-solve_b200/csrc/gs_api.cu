@@ -633,15 +633,22 @@ int zero_field(gs_handle* h, Level& L, double* a)
 
 // first level of the coarse tail (run as one single-CTA kernel, kernels_simple.cu ks_tail_*), or -1.  Never the
 // coarsest level alone (nothing to merge), not on slabs, not while per-operator events are wanted.
-int tail_first_level(const gs_handle* h)
+int plan_tail(const gs_params& p, i64 tail_points)
 {
-    if (h->cx.tune.tail_points <= 0 || h->world != 1 || h->opt_timing) return -1;
-    const int last = (int)h->lev.size() - 1;
+    if (tail_points <= 0) return -1;
+    const int last = num_levels_for(p) - 1;
     for (int l = 0; l < last; l++) {
-        const Geom& g = h->lev[l].g;
-        if ((i64)g.nx * g.ny * g.nz <= (i64)h->cx.tune.tail_points) return l;
+        uint64_t n[3];
+        level_dims(p, l, n);
+        if ((i64)(n[0] * n[1] * n[2]) <= tail_points) return l;
     }
     return -1;
+}
+
+int tail_first_level(const gs_handle* h)
+{
+    if (h->world != 1 || h->opt_timing) return -1;
+    return plan_tail(h->p, h->cx.tune.tail_points);
 }
 
 int tail_begin(gs_handle* h)
@@ -1285,6 +1292,13 @@ int gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int ove
     LaunchCtx cx{};
     cx.sm_count = sm_count;
     return gs_pick_zchunk_waves(cx, tiles, planes, ctas_per_sm, overhead, min_chunk, max_chunk, even != 0);
+}
+
+int gs_plan_tail(const gs_params* p, int64_t tail_points)
+{
+    if (!p) return fail(GS_EINVAL, "null argument");
+    GS(validate(*p));
+    return plan_tail(*p, tail_points);
 }
 
 int gs_num_levels(const gs_handle* h) { return h ? (int)h->lev.size() : fail(GS_EINVAL, "null handle"); }

@@ -129,6 +129,11 @@ int  gs_partition(const gs_params* p, int world, int rank, int level,
 int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int overhead,
                     int min_chunk, int max_chunk, int even);
 
+/* first level of the coarse tail for option "tail_points" = tail_points (levels of at most that many interior points
+ * run as one single-CTA kernel per V-cycle), pure host arithmetic: -1 = no tail (off, or only the coarsest level fits);
+ * a negative GS_E* code below -1 never occurs for valid params */
+int  gs_plan_tail(const gs_params* p, int64_t tail_points);
+
 /* ---- introspection: CpuGridData::numLevels / getLevel (src/cpu/CpuGridData.h:22-33) */
 int  gs_num_levels(const gs_handle* h);
 int  gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hval);

@@ -232,3 +232,16 @@ def test_partition_invariants_on_random_grids(gs):
     for _ in range(300):
         n = tuple(rnd.randint(1, 1200) for _ in range(3))
         _check_partition(gs, n, rnd.randint(2, 8))
+
+
+def test_coarse_tail_selection(gs):
+    """which levels the option "tail_points" hands to the single-CTA kernel (gs_plan_tail, host arithmetic)"""
+    assert gs.plan_tail(gs.make_params(511), 0) == -1                 # off
+    assert gs.plan_tail(gs.make_params(511), 4096) == 5               # 511 255 127 63 31 [15 7 3 1]
+    assert gs.plan_tail(gs.make_params(511), 40000) == 4              # from 31^3
+    assert gs.plan_tail(gs.make_params(127), 4096) == 3               # the shipped config: 127 63 31 [15 7 3 1]
+    assert gs.plan_tail(gs.make_params(15), 4096) == 0                # the whole cycle
+    assert gs.plan_tail(gs.make_params(1), 4096) == -1                # a single level: nothing to merge
+    assert gs.plan_tail(gs.make_params(3), 1) == -1                   # only the coarsest level fits
+    assert gs.plan_tail(gs.make_params((40, 30, 50)), 10000) == 1     # 20 x 15 x 25 = 7500
+    assert gs.plan_tail(gs.make_params(4000), 1 << 20) == 6           # 4000 2000 1000 500 250 125 [62 ...]
