@@ -263,3 +263,67 @@ def producer_ring(nz, nwarps=4, seed=0, ns=4):
 
     sim.run([producer()] + [warp(w) for w in range(nwarps)])
     return sim
+
+
+# ---------------------------------------------------------------------------------
+# design study for the next round: prolongation+correction folded into the two-sweep post-smoother.
+# Plane P lands uncorrected; at step q every warp adds the interpolated correction to ITS points of plane q+2 in place,
+# before the arrival that ends the step.  The plane is read as U (own points) at step q+1 and as E/W/S/N (other warps'
+# points) at step q+2 — behind the wait of step q+1, which proves every warp has finished step q.  No new barrier.
+# ---------------------------------------------------------------------------------
+def smooth2_prolong(nzo, nwarps=4, seed=0, ns=6, correct_ahead=2):
+    sim = Sim(ns, 2, nwarps, seed)
+    s1bar = MBar(nwarps)
+    last, top = nzo + 2, nzo + 3
+    corrected = [[None] * nwarps for _ in range(ns)]   # per stage and warp: plane whose correction that warp has stored
+
+    def correct(w, P):
+        if P > top:
+            return
+        sim.read_stage(P % ns, P, f"warp {w} correction of plane {P}")
+        corrected[P % ns][w] = P
+
+    def read_corrected(w, P, own, who):
+        sim.read_stage(P % ns, P, who)
+        ws = [w] if own else range(nwarps)
+        bad = [x for x in ws if corrected[P % ns][x] != P]
+        if bad:
+            raise Hazard(f"{who}: plane {P} read before warps {bad} corrected it")
+
+    def warp(w):
+        if w == 0:
+            for P in range(min(ns, top + 1)):
+                sim.issue(P % ns, P)
+        yield sim.cta_barrier(w)
+        # prologue: planes 0 .. correct_ahead are corrected behind a CTA barrier of their own
+        for P in range(0, correct_ahead + 1):
+            yield _wait(sim.full[P % ns], (P // ns) & 1)
+            correct(w, P)
+        yield sim.cta_barrier(w)
+        read_corrected(w, 0, True, f"warp {w} prologue")
+        read_corrected(w, 1, True, f"warp {w} prologue")
+        for q in range(1, last + 1):
+            P = q + correct_ahead
+            if P <= top and P > correct_ahead:
+                yield _wait(sim.full[P % ns], (P // ns) & 1)
+                correct(w, P)
+                yield None
+            read_corrected(w, q + 1, True, f"warp {w} step {q} (U)")
+            read_corrected(w, q, False, f"warp {w} step {q} (E/W/S/N)")
+            yield None
+            if q >= 2:
+                yield _wait(s1bar, q & 1)
+                if w == 0:
+                    if q == 2 and ns <= top:
+                        sim.issue(0, ns)
+                    if q + ns - 1 <= top:
+                        sim.issue((q + ns - 1) % ns, q + ns - 1)
+            if q >= 3:
+                sim.read_slot((q - 1) & 1, q - 1, f"warp {w} second sweep of plane {q - 1}")
+                yield None
+            sim.write_slot(q & 1, q, w)
+            s1bar.arrive()
+            yield None
+
+    sim.run([warp(w) for w in range(nwarps)])
+    return sim
