@@ -8,11 +8,7 @@ import numpy as np
 CANON = (6.0, -1.0, -1.0, -1.0, -1.0, -1.0, -1.0)
 
 
-def jacobi_sweep(v, f, h, omega, zb, ze, c=CANON):
-    """one damped-Jacobi sweep of the interior points of LOCAL planes [zb, ze) of v ([z,y,x], halo included);
-    returns (new array, sum r^2 over the updated points)"""
-    hh = h * h
-    alpha = hh / c[0]
+def _tap_sum(v, zb, ze, c):
     C = v[zb:ze, 1:-1, 1:-1]
     s = 0.0 + c[0] * C
     s = s + c[1] * v[zb:ze, 1:-1, 2:]
@@ -21,9 +17,39 @@ def jacobi_sweep(v, f, h, omega, zb, ze, c=CANON):
     s = s + c[4] * v[zb:ze, :-2, 1:-1]
     s = s + c[5] * v[zb + 1:ze + 1, 1:-1, 1:-1]
     s = s + c[6] * v[zb - 1:ze - 1, 1:-1, 1:-1]
-    r = f[zb:ze, 1:-1, 1:-1] - s / hh
+    return C, s
+
+
+def _residual(v, f, h, zb, ze, c, mode, gamma, aux):
+    """(centre values, r, Jacobi denominator or None) on the interior of LOCAL planes [zb, ze):
+    src/cpu/CpuSolver.cpp:56-74 and :161-171 in the operation order of gs_device.cuh finish_residual"""
+    hh = h * h
+    C, s = _tap_sum(v, zb, ze, c)
+    s = s / hh
+    den = None
+    if mode == 1:
+        ex = np.exp(C)
+        s = s + (gamma * C) * ex
+        den = c[0] / hh + (gamma * (1 + C)) * ex
+    elif mode == 2:
+        A = aux[zb:ze, 1:-1, 1:-1]
+        ex = np.exp(A)
+        g1 = gamma * (1 + A)
+        s = s + (g1 * C) * ex
+        den = c[0] / hh + g1 * ex
+    return C, f[zb:ze, 1:-1, 1:-1] - s, den
+
+
+def jacobi_sweep(v, f, h, omega, zb, ze, c=CANON, mode=0, gamma=1.0, aux=None):
+    """one damped-Jacobi sweep of the interior points of LOCAL planes [zb, ze) of v ([z,y,x], halo included);
+    returns (new array, sum r^2 over the updated points)"""
+    C, r, den = _residual(v, f, h, zb, ze, c, mode, gamma, aux)
     out = v.copy()
-    out[zb:ze, 1:-1, 1:-1] = C + omega * (alpha * r)
+    if mode == 0:
+        alpha = (h * h) / c[0]
+        out[zb:ze, 1:-1, 1:-1] = C + omega * (alpha * r)
+    else:
+        out[zb:ze, 1:-1, 1:-1] = C + omega * (r / den)
     return out, float(np.sum(r * r))
 
 
@@ -146,20 +172,18 @@ def worker(rank, world, port, n, seed, out_path):
 # whole V-cycle on slabs (linear mode): the data flow of gs_api.cu enqueue_vcycle with world > 1 — partitioned fine
 # levels, the first replicated level gathered from the slabs, everything below computed by every rank
 # ---------------------------------------------------------------------------------------------------------------
-def residual_planes(v, f, h, zb, ze, c=CANON):
+def residual_planes(v, f, h, zb, ze, c=CANON, mode=0, gamma=1.0, aux=None):
     """r = f - A v on the interior points of LOCAL planes [zb, ze), zero elsewhere (src/cpu/CpuSolver.cpp:45-83)"""
-    hh = h * h
-    C = v[zb:ze, 1:-1, 1:-1]
-    s = 0.0 + c[0] * C
-    s = s + c[1] * v[zb:ze, 1:-1, 2:]
-    s = s + c[2] * v[zb:ze, 1:-1, :-2]
-    s = s + c[3] * v[zb:ze, 2:, 1:-1]
-    s = s + c[4] * v[zb:ze, :-2, 1:-1]
-    s = s + c[5] * v[zb + 1:ze + 1, 1:-1, 1:-1]
-    s = s + c[6] * v[zb - 1:ze - 1, 1:-1, 1:-1]
     r = np.zeros_like(v)
-    r[zb:ze, 1:-1, 1:-1] = f[zb:ze, 1:-1, 1:-1] - s / hh
+    r[zb:ze, 1:-1, 1:-1] = _residual(v, f, h, zb, ze, c, mode, gamma, aux)[1]
     return r
+
+
+def fas_rhs_planes(restv, h, zb, ze, gamma, c=CANON):
+    """A(restV)/hh + gamma*restV*exp(restV) on the interior of LOCAL planes [zb, ze) (src/cpu/CpuSolver.cpp:182-209)"""
+    C, s = _tap_sum(restv, zb, ze, c)
+    s = s / (h * h)
+    return s + (gamma * C) * np.exp(C)
 
 
 def restrict_planes(fine, z0f, cb, ce, cshape):
@@ -218,17 +242,20 @@ class MgLevel:
         shape = (self.z1 - self.z0, self.ny + 2, self.nx + 2)
         self.v = np.zeros(shape)
         self.f = np.zeros(shape)
+        self.restV = np.zeros(shape)   # mode 1
+        self.nv = np.zeros(shape)      # mode 2: the frozen Newton iterate of the level
         self.gv = 2
         self.ib = max(1, self.zlo) - self.z0          # owned interior planes, local
         self.ie = min(self.nz + 1, self.zhi) - self.z0
 
 
 class SlabMultigrid:
-    def __init__(self, dist, rank, world, n, levels, rep, pre=2, post=2, omega=0.8, overlap=False):
+    def __init__(self, dist, rank, world, n, levels, rep, pre=2, post=2, omega=0.8, overlap=False, mode=0, gamma=1.0):
         """levels: [(zlo, zhi)] per level from gs_partition; rep: first replicated level; overlap: the ghost refresh
         runs "beside" the interior launch of the operator that needs it (gs_api.cu halo_begin / halo_end)"""
         self.dist, self.rank, self.world = dist, rank, world
         self.overlap, self.overlapped = overlap, 0
+        self.mode, self.gamma = mode, gamma
         self.pre, self.post, self.omega = pre, post, omega
         self.lev = []
         dims = (n, n, n) if isinstance(n, int) else tuple(n)[::-1]   # (nz, ny, nx)
@@ -300,8 +327,9 @@ class SlabMultigrid:
         hi = min(ze + 1, L.nz + 1 - L.z0)
         src = L.v[zb - 2 if zb >= 2 else 0:ze + 2]
         off = zb - 2 if zb >= 2 else 0
-        mid, _ = jacobi_sweep(src, L.f[off:ze + 2], L.h, self.omega, lo - off, hi - off)
-        res, _ = jacobi_sweep(mid, L.f[off:ze + 2], L.h, self.omega, zb - off, ze - off)
+        kw = dict(mode=self.mode, gamma=self.gamma, aux=L.nv[off:ze + 2])
+        mid, _ = jacobi_sweep(src, L.f[off:ze + 2], L.h, self.omega, lo - off, hi - off, **kw)
+        res, _ = jacobi_sweep(mid, L.f[off:ze + 2], L.h, self.omega, zb - off, ze - off, **kw)
         out[zb:ze] = res[zb - off:ze - off]
 
     def smooth(self, l, iters):
@@ -329,11 +357,12 @@ class SlabMultigrid:
                 # two sweeps per pass: the first also updates the ghost plane next to the slab (if it is interior)
                 lo = L.ib - 1 if (self.part(l) and L.zlo > 1) else L.ib
                 hi = L.ie + 1 if (self.part(l) and L.zhi < L.Z - 1) else L.ie
-                mid, _ = jacobi_sweep(L.v, L.f, L.h, self.omega, lo, hi)
-                L.v, _ = jacobi_sweep(mid, L.f, L.h, self.omega, L.ib, L.ie)
+                kw = dict(mode=self.mode, gamma=self.gamma, aux=L.nv)
+                mid, _ = jacobi_sweep(L.v, L.f, L.h, self.omega, lo, hi, **kw)
+                L.v, _ = jacobi_sweep(mid, L.f, L.h, self.omega, L.ib, L.ie, **kw)
                 iters -= 2
             else:
-                L.v, _ = jacobi_sweep(L.v, L.f, L.h, self.omega, L.ib, L.ie)
+                L.v, _ = jacobi_sweep(L.v, L.f, L.h, self.omega, L.ib, L.ie, mode=self.mode, gamma=self.gamma, aux=L.nv)
                 iters -= 1
             L.gv = 0
 
@@ -352,7 +381,7 @@ class SlabMultigrid:
             """fused residual+restriction onto GLOBAL coarse planes [b, e): reads fine v planes 2b-2 .. 2e"""
             rb = max(1, 2 * b - 1) - F.z0
             re = min(F.nz + 1, 2 * e) - F.z0
-            r = residual_planes(F.v, F.f, F.h, rb, re)
+            r = residual_planes(F.v, F.f, F.h, rb, re, mode=self.mode, gamma=self.gamma, aux=F.nv)
             C.f[b - C.z0:e - C.z0] = restrict_planes(r, F.z0, b, e, (C.ny + 2, C.nx + 2))
 
         lo_b = 4 if F.zlo > 0 else 0
@@ -369,10 +398,31 @@ class SlabMultigrid:
             if self.part(l):
                 self.need_v_halo(l, 2)   # the lowest owned coarse plane needs r one fine plane below the slab
             launch(cb, ce)
+        self.finish_coarse(l, C.f)
+
+    def finish_coarse(self, l, coarse):
+        """gs_api.cu finish_coarse: gather on the first replicated level, else one ghost plane per side"""
+        C = self.lev[l + 1]
         if self.part(l) and C.replicated:
-            self.gather_planes(l, C.f)
+            self.gather_planes(l, coarse)
         elif self.part(l + 1):
-            self.exchange(l + 1, C.f, 1)
+            self.exchange(l + 1, coarse, 1)
+
+    def fas_coarse_rhs(self, l):
+        """gs_api.cu do_fas_coarse_rhs (src/cpu/CpuSolver.cpp:106-112): restV = v_coarse = R v; f_coarse += A(restV)"""
+        F, C = self.lev[l], self.lev[l + 1]
+        self.need_v_halo(l, 1)
+        cb, ce = self.coarse_range(l)
+        got = restrict_planes(F.v, F.z0, cb, ce, (C.ny + 2, C.nx + 2))
+        C.restV[cb - C.z0:ce - C.z0] = got
+        C.v[cb - C.z0:ce - C.z0] = got
+        self.finish_coarse(l, C.restV)
+        self.finish_coarse(l, C.v)
+        C.gv = 1
+        s = fas_rhs_planes(C.restV, C.h, C.ib, C.ie, self.gamma)
+        C.f[C.ib:C.ie, 1:-1, 1:-1] = C.f[C.ib:C.ie, 1:-1, 1:-1] + s
+        if self.part(l + 1):
+            self.exchange(l + 1, C.f, 1)   # f changed on the owned planes only
 
     def gather_planes(self, l, coarse):
         """gs_comm_gather_planes: every rank broadcasts the coarse planes it computed"""
@@ -387,6 +437,9 @@ class SlabMultigrid:
     def prolong_correct(self, l):
         F, C = self.lev[l], self.lev[l + 1]
         self.need_v_halo(l + 1, 1)   # the interpolation reads one coarse plane outside the slab
+        if self.mode == 1:
+            C.v = C.v - C.restV      # all local planes; restV carries one current ghost plane
+            C.gv = min(C.gv, 1)
         zb, ze = F.ib + F.z0, F.ie + F.z0
         e = prolong_planes(C.v, C.z0, zb, ze, F.ny, F.nx)
         F.v[F.ib:F.ie, 1:-1, 1:-1] = F.v[F.ib:F.ie, 1:-1, 1:-1] + e
@@ -400,22 +453,25 @@ class SlabMultigrid:
             self.smooth(i, self.pre)
             self.restrict_residual(i)
             C = self.lev[i + 1]
-            C.v[...] = 0.0
-            C.gv = 2
+            if self.mode != 1:
+                C.v[...] = 0.0
+                C.gv = 2
+            else:
+                self.fas_coarse_rhs(i)
         self.smooth(last, self.pre + self.post)
         for i in range(last, 0, -1):
             self.prolong_correct(i - 1)
             self.smooth(i - 1, self.post)
         L = self.lev[0]
         self.need_v_halo(0, 1)
-        r = residual_planes(L.v, L.f, L.h, L.ib, L.ie)
+        r = residual_planes(L.v, L.f, L.h, L.ib, L.ie, mode=self.mode, gamma=self.gamma, aux=L.nv)
         t = torch.tensor([float(np.sum(r * r))], dtype=torch.float64)
         if self.part(0):
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
         return t.item()
 
 
-def vcycle_worker(rank, world, port, n, seed, cycles, out_path, overlap=False):
+def vcycle_worker(rank, world, port, n, seed, cycles, out_path, overlap=False, mode=0):
     """gloo process `rank`: `cycles` V(2,2) cycles of a seeded level-0 problem on slabs; rank 0 saves the gathered v"""
     import os
     import sys
@@ -436,13 +492,16 @@ def vcycle_worker(rank, world, port, n, seed, cycles, out_path, overlap=False):
         for l in range(nlev):
             zlo, zhi, rep = gs.partition(p, world, rank, l)
             levels.append((zlo, zhi))
-        mg = SlabMultigrid(dist, rank, world, n, levels, rep, overlap=overlap)
+        mg = SlabMultigrid(dist, rank, world, n, levels, rep, overlap=overlap, mode=mode)
         shape = (n + 2, n + 2, n + 2)
         v = seeded_field(shape, seed)
         f = seeded_field(shape, seed + 1, scale=1.0)
         L = mg.lev[0]
         L.v[...] = v[L.z0:L.z1]
         L.f[...] = f[L.z0:L.z1]
+        if mode == 2:   # a frozen Newton iterate on every level, ghost planes included (gs_set_field)
+            for l, M in enumerate(mg.lev):
+                M.nv[...] = seeded_field((M.Z, M.ny + 2, M.nx + 2), seed + 10 + l)[M.z0:M.z1]
         sums = [mg.vcycle() for _ in range(cycles)]
         parts = [None] * world
         dist.all_gather_object(parts, (L.zlo, L.zhi, L.v[L.zlo - L.z0:L.zhi - L.z0]))

@@ -101,3 +101,32 @@ def test_overlapped_ghost_refresh_keeps_the_bits(oracle_mod, tmp_path, monkeypat
     o.vcycle()
     assert np.array_equal(got["v"], o.get(0, V))
     o.close()
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+def test_slab_vcycles_in_the_exp_modes(oracle_mod, tmp_path, monkeypatch, mode):
+    """FAS (two-output restriction, coarse right-hand side from restV, v -= restV before the prolongation) and the Newton
+    inner cycle on three slabs — a rank with neighbours on both sides.  numpy's exp is not glibc's, so bit equality is
+    asked between the slab run and the same model on one rank (what sharding must not change), and 1e-12 against the
+    oracle (north_star's tolerance for the exp() modes)"""
+    import torch.multiprocessing as mp
+    monkeypatch.setenv("GPUSOLVE_SLAB_MIN_POINTS", "1000")
+    n, cycles = 63, 2
+    outs = []
+    for world in (3, 1):
+        out = str(tmp_path / f"mg{world}.npz")
+        mp.spawn(slab_model.vcycle_worker, args=(world, _free_port(), n, 41, cycles, out, False, mode), nprocs=world, join=True)
+        outs.append(np.load(out))
+    assert int(outs[0]["rep"]) >= 2 and int(outs[1]["rep"]) == 0
+    assert np.array_equal(outs[0]["v"], outs[1]["v"]), "sharding changed the bits"
+    o = oracle_mod.Oracle(oracle_mod.make_params(n, mode=mode, pre=2, post=2, maxiter=1, tol=1e-30), "port")
+    o.set(0, V, seeded_field(o.shape(0), 41))
+    o.set(0, F, seeded_field(o.shape(0), 42, scale=1.0))
+    if mode == 2:
+        for l in range(o.num_levels):
+            o.set(l, 5, seeded_field(o.shape(l), 51 + l))
+    norms = [o.vcycle() for _ in range(cycles)]
+    want = o.get(0, V)
+    assert np.abs(outs[1]["v"] - want).max() <= 1e-12 * np.abs(want).max()
+    assert abs(np.sqrt(outs[1]["sums"][-1]) - norms[-1]) <= 1e-11 * norms[-1]
+    o.close()
