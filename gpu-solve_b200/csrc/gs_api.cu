@@ -640,7 +640,7 @@ int plan_tail(const gs_params& p, i64 tail_points)
     for (int l = 0; l < last; l++) {
         uint64_t n[3];
         level_dims(p, l, n);
-        if ((i64)(n[0] * n[1] * n[2]) <= tail_points) return l;
+        if ((i64)(n[0] * n[1] * n[2]) <= tail_points && last - l + 1 <= GS_TAIL_MAX_LEVELS) return l;
     }
     return -1;
 }

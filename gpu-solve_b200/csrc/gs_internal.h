@@ -72,6 +72,7 @@ struct Tune {
 };
 
 struct TailRec;  // kernels_simple.cu: the operator list of the coarse tail of a V-cycle
+constexpr int GS_TAIL_MAX_LEVELS = 6;  // levels one tail program can address (its level table travels in the kernel parameters)
 
 struct LaunchCtx {
     cudaStream_t stream;

@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(BX* BY) init_rhs_simple(Geom g, int mode, doub
 // coarse tail: a recorded list of the operators above, run by ONE CTA (gs_internal.h ks_tail_*)
 // ---------------------------------------------------------------------------------
 enum { T_SMOOTH, T_RESID, T_RESTRICT, T_PROLONG, T_FAS, T_COEF, T_AXPY, T_ZERO, T_COPY };
-constexpr int TAIL_THREADS = 1024, TAIL_MAX_OPS = 96, TAIL_MAX_LEV = 12;
+constexpr int TAIL_THREADS = 1024, TAIL_MAX_OPS = 44, TAIL_MAX_LEV = GS_TAIL_MAX_LEVELS;
 
 struct TailLev {
     Geom g;
@@ -343,14 +343,16 @@ struct TailLev {
 };
 
 struct TailOp {
-    int type, pow2;
-    int la, lb;   // level-table entries: the level (fine level of a transfer), the coarse level of a transfer
-    int zb, nz;   // first local plane and number of planes of the points to visit
-    int sign, pad;
+    unsigned char type, pow2;
+    unsigned char la, lb;  // level-table entries: the level (fine level of a transfer), the coarse level of a transfer
+    int sign;
+    int zb, nz;            // first local plane and number of planes of the points to visit
     const double *a, *b, *c;  // inputs, in the order of the ks_* signature
     double *o, *o2;           // outputs
-    double gamma;
-    i64 count;                // T_ZERO / T_COPY: doubles
+    union {
+        double gamma;  // T_COEF
+        i64 count;     // T_ZERO / T_COPY: doubles
+    };
 };
 
 struct TailProg {
@@ -358,7 +360,9 @@ struct TailProg {
     TailLev lev[TAIL_MAX_LEV];
     TailOp op[TAIL_MAX_OPS];
 };
-static_assert(sizeof(TailProg) < 30000, "the program is passed as a kernel parameter (32764-byte limit)");
+// the program is passed as a kernel parameter and stays inside the classic 4 KB parameter space (no reliance on the
+// 32 KB limit of newer drivers): a V(3,3) tail of four levels is 37 operators; longer ones are split by the recorder
+static_assert(sizeof(TailOp) == 64 && sizeof(TailProg) <= 4096, "tail program must fit the 4 KB kernel parameter space");
 
 // visit the nx*ny*nz points of planes [zb, zb+nz), x fastest, nthr at a time
 template <typename F>

@@ -86,10 +86,10 @@ def test_skewed_stencil_through_the_tail(harness, oracle_mod):
 
 
 def test_long_programs_are_split_not_truncated(harness, oracle_mod):
-    """V(30,30) on four levels is more than the 96 operators one program holds: the recorder launches what it has and
+    """V(30,30) on four levels is more than the 44 operators one program holds: the recorder launches what it has and
     starts the next program; the result must not change"""
     got, want, programs, ops, nlev = run_case(harness, oracle_mod, 15, 0, 30, 30, 0, cycles=1)
-    assert ops > 96 and programs == (ops + 95) // 96
+    assert ops > 44 and programs == (ops + 43) // 44
     assert np.array_equal(got, want)
 
 
