@@ -19,4 +19,6 @@ for n in 63 127 255; do
         env $cfg timeout 60 python tools/profile_levels.py --n $n > $out/${tag}_levels_n${n}_${name}.txt 2>&1
     done
 done
+# small-level thresholds once more, now that the per-level launch costs have changed
+bash tools/gpu_variants.sh ${tag}_thr "fuse2_min_n=64" "fast_min_n=32" "fuse2_min_n=64 fast_min_n=32" "tail_points=4096 fuse2_min_n=64"
 echo done
