@@ -6,15 +6,25 @@ V(2,2), BASELINE.json configs[1]) with the fine-level smoother against the HBM r
   python bench.py --impl reference ...                      the reference's own CPU path on the host cores
 
 A step is one V(2,2) cycle of the hot path (including the per-cycle residual norm the reference's
-solve loop reads back).  One JSON line on stdout (rank 0).  N > 1: one process per GPU under
-torchrun, the grid is split into z-slabs (strong scaling of the same grid), NCCL halo exchange.
+solve loop reads back).  One JSON line on stdout (rank 0).
+
+N = 1: the 513^3 grid.  N > 1 (one process per GPU under torchrun): WEAK scaling by default — the same lattice
+points per GPU (511x511x1023, 511x1023x1023, 1023^3 at N = 2, 4, 8), split into z-slabs; `value` is then the whole
+job's throughput in 513^3-EQUIVALENT V-cycles/s (cycles/s on the grid x its lattice points / those of 513^3) and the
+metric string says so.  `--grid 1023` gives the strong-scaling run of BASELINE.json configs[4]; every N > 1 line also
+carries a `strong_1023` sub-record (1023^3 on N GPUs against 1023^3 on one GPU of the same box) and a `slab_parity`
+record (slab run == one-GPU run bit for bit, checked before anything is timed).
+
+What the fractions mean (VERDICT r01 "weak" 3): `roofline.frac` is a BANDWIDTH fraction — the compulsory bytes of one
+pass of the dominant kernel (read v, read f, write v'' once: 24 B per point, 32 in mode 2) / its time / the measured
+copy peak — and is <= ~1.  That a pass applies two Jacobi sweeps shows up in `glups` and `lup_equivalent_gbs`
+(24 B per lattice UPDATE / time), not in `frac`.  `vcycle.frac_of_peak` is per GPU and counts the passes launched.
 """
 import argparse
 import json
 import os
 import subprocess
 import sys
-import tempfile
 import threading
 import time
 
@@ -37,11 +47,28 @@ def interior_points(n, levels=None):
 
 
 def vcycle_algorithmic_bytes(n, pre, post, mode=0):
-    """B_V = sum_{l<L-1} P_l [24(v1+v2) + 17 + 17] + P_{L-1} 24 (v1+v2) + 24 P_0 (mode 2: 32/25)"""
+    """B_V = sum_{l<L-1} P_l [24(v1+v2) + 17 + 17] + P_{L-1} 24 (v1+v2) + 24 P_0 (mode 2: 32/25).
+    One pass per operator the REFERENCE applies — the figure the survey's bound is quoted on."""
     P = interior_points(n)
     sweep = 32 if mode == 2 else 24
     rr = 25 if mode == 2 else 17
     b = sum(p * (sweep * (pre + post) + rr + 17) for p in P[:-1]) + P[-1] * sweep * (pre + post) + sweep * P[0]
+    return b
+
+
+def pass_level_bytes(n, mode, level_launches):
+    """Compulsory traffic of the passes actually LAUNCHED in one cycle: every smoother / residual-norm launch reads v
+    and f (and the Newton coefficient) and writes v once (24 / 32 B per point however many sweeps it applies), the
+    fused residual+restriction 17 / 25 B per fine point, prolongation+correction 17.  level_launches[l] = {op:
+    launches per cycle}."""
+    P = interior_points(n)
+    sweep = 32 if mode == 2 else 24
+    rr = 25 if mode == 2 else 17
+    b = 0.0
+    for l, ops in enumerate(level_launches):
+        b += P[l] * sweep * (ops.get("smooth", 0) + ops.get("residual", 0))
+        b += P[l] * rr * min(ops.get("restrict", 0), 1)
+        b += P[l] * 17 * min(ops.get("prolong", 0), 1)
     return b
 
 
@@ -104,40 +131,91 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_sample_grid(n, steps_total, cores, budget_s):
-    """the largest grid, obtained by halving the target like the hierarchy does, whose CPU run fits the budget
-    (one 511^3 V(2,2) cycle is ~9 s on 8 cores)"""
+# ---------------------------------------------------------------------------------------------------------------------
+# the reference's CPU path on the host cores (oracle/_ref when built, else the C port)
+# ---------------------------------------------------------------------------------------------------------------------
+def host_ram_gb():
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+def cpu_grid_ram_gb(n):
+    """six (n+2)^3 arrays per level (src/cpu/CpuGridData.cpp:32-39) plus newtonF and slack"""
+    return 8.0 * (n[0] + 2) * (n[1] + 2) * (n[2] + 2) * 6 * 1.15 / 1e9
+
+
+def cpu_sample_grid(n, steps_total, cores, budget_s, per_cycle_511_8cores=3.6):
+    """the largest grid, obtained by halving the target like the hierarchy does, whose CPU run fits the time budget
+    (one 511^3 V(2,2) cycle of the LTO-built reference is ~3.6 s on 8 cores)"""
     n = tuple(n)
-    est = 9.0 * (n[0] * n[1] * n[2]) / 511.0 ** 3 * 8.0 / max(cores, 1) * steps_total
+    est = per_cycle_511_8cores * (n[0] * n[1] * n[2]) / 511.0 ** 3 * 8.0 / max(cores, 1) * steps_total
     while min(n) > 63 and est > budget_s:
         n = tuple((d + 1) // 2 - 1 for d in n)
         est /= 8.0
     return n
 
 
-def run_cpu(n, pre, post, steps, warm, budget_s):
-    """the reference's CPU V-cycle (oracle/_ref when built, else the C port) on all host threads; returns
-    (V-cycles/s on grid n, kind, cores, sample description)"""
+def cpu_oracle():
     orc = entry.load_oracle()
     kind = "reference" if orc.available("reference") else "port"
     if kind == "port" and not orc.available("port"):
         orc.build(ref=False)
+    return orc, kind
+
+
+def run_cpu(n, pre, post, steps, warm, budget_s, mode=0):
+    """Times the reference's CPU V-cycle on all host threads.  Never shrinks the grid silently: if `steps + warm` cycles
+    of grid n do not fit the budget it first runs FEWER cycles of the stated grid (at least one warm-up and one timed),
+    and only if even that does not fit (or the grid does not fit host memory) it runs a smaller grid and says so
+    (`extrapolated`).  Returns a dict."""
+    orc, kind = cpu_oracle()
     cores = os.cpu_count()
-    sn = cpu_sample_grid(n, steps + warm, cores, budget_s)
-    o = orc.Oracle(orc.make_params(sn, mode=0, pre=pre, post=post, maxiter=1, tol=1e-30), kind)
+    n = tuple(n)
+    # calibrate the cost per lattice point on a grid that takes a fraction of a second
+    cal = cpu_sample_grid(n, 2, cores, 1.5)
+    o = orc.Oracle(orc.make_params(cal, mode=mode, pre=pre, post=post, maxiter=1, tol=1e-30), kind)
     o.set_threads(cores)
-    for _ in range(warm):
+    o.vcycle()
+    t0 = time.time()
+    o.vcycle()
+    per_pt = (time.time() - t0) / sum(interior_points(cal))
+    o.close()
+    est = per_pt * sum(interior_points(n))            # seconds per cycle on the stated grid
+    sn, run_steps, run_warm, extrapolated = n, steps, warm, False
+    fits_ram = cpu_grid_ram_gb(n) < 0.8 * host_ram_gb()
+    if not fits_ram or est * 2 > budget_s:
+        extrapolated = True
+        while min(sn) > 63 and (cpu_grid_ram_gb(sn) >= 0.8 * host_ram_gb() or per_pt * sum(interior_points(sn)) * 2 > budget_s):
+            sn = tuple((d + 1) // 2 - 1 for d in sn)
+        est = per_pt * sum(interior_points(sn))
+    total = max(2, int(budget_s / max(est, 1e-9)))
+    if run_steps + run_warm > total:
+        run_warm = max(1, min(run_warm, total // 4)) if warm > 0 else (1 if total > 1 else 0)
+        run_steps = max(1, min(steps, total - run_warm))
+    o = orc.Oracle(orc.make_params(sn, mode=mode, pre=pre, post=post, maxiter=1, tol=1e-30), kind)
+    o.set_threads(cores)
+    for _ in range(run_warm):
         o.vcycle()
     t0 = time.time()
-    for _ in range(steps):
+    for _ in range(run_steps):
         o.vcycle()
     dt = time.time() - t0
     o.close()
-    scale = sum(interior_points(sn)) / sum(interior_points(tuple(n)))
-    desc = (f"{steps} V({pre},{post}) cycle(s) of GpuSolve-cpu ({kind}) at n={'x'.join(map(str, sn))} on {cores} OpenMP threads: "
-            f"{dt / steps:.2f} s per cycle" + ("" if tuple(sn) == tuple(n) else f"; throughput scaled by lattice points x{scale:.5f} "
-                                               f"to n={'x'.join(map(str, n))}"))
-    return steps / dt * scale, kind, cores, desc
+    scale = sum(interior_points(sn)) / sum(interior_points(n))
+    gname = "x".join(map(str, sn))
+    desc = (f"{run_steps} timed V({pre},{post}) cycle(s) after {run_warm} warm-up of GpuSolve-cpu ({kind}, -O3 -flto, OpenMP) at n={gname} "
+            f"on {cores} threads: {dt / run_steps:.3f} s per cycle")
+    if extrapolated:
+        desc += (f"; EXTRAPOLATED to n={'x'.join(map(str, n))} by lattice points (x{scale:.5f}): the stated grid needs "
+                 f"{cpu_grid_ram_gb(n):.0f} GB / ~{per_pt * sum(interior_points(n)):.0f} s per cycle on this host")
+    return {"cycles_per_s": run_steps / dt * scale, "kind": kind, "cores": cores, "sample": desc, "extrapolated": extrapolated,
+            "grid_run": list(sn), "steps_run": run_steps, "warmup_run": run_warm, "s_per_cycle_run": dt / run_steps}
 
 
 def run_reference_arm(args, emit):
@@ -145,15 +223,16 @@ def run_reference_arm(args, emit):
     if rank != 0:
         return 0
     n, pre, post = resolve_grid(args), args.pre, args.post
-    steps, warm = args.steps, args.warmup
-    v, kind, cores, sample = run_cpu(n, pre, post, steps, warm, budget_s=150.0)
-    value = v * work_ratio(n)
+    r = run_cpu(n, pre, post, args.steps, args.warmup, budget_s=150.0)
+    value = r["cycles_per_s"] * work_ratio(n)
     line = {
-        "impl": "reference", "metric": "V-cycles/s at 513^3 fp64, linear V(2,2)", "value": value, "unit": "V-cycles/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 / v,
+        "impl": "reference", "metric": metric_name(args, n), "value": value, "unit": "V-cycles/s",
+        "n_gpus": args.gpus, "steps": r["steps_run"], "warmup": r["warmup_run"], "steps_requested": args.steps, "warmup_requested": args.warmup,
+        # wall time per step of what actually ran (so steps x ms_per_step is the real timed region)
+        "ms_per_step": 1e3 * r["s_per_cycle_run"], "extrapolated": r["extrapolated"], "grid_run": r["grid_run"],
         "higher_is_better": True, "scaling": "weak" if args.grid is None else "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (analytic RHS)", "config": workload_config(args),
-        "cpu_baseline": {"value": value, "unit": "V-cycles/s", "cores": cores, "kind": kind, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "V-cycles/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
         "e2e": {"value": value, "unit": "V-cycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -161,6 +240,9 @@ def run_reference_arm(args, emit):
     return 0
 
 
+# ---------------------------------------------------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------------------------------------------------
 REF_GRID = (511, 511, 511)   # BASELINE.json configs[1]: "513^3" = 511 interior points per axis
 
 
@@ -191,6 +273,16 @@ def work_ratio(n):
     return sum(interior_points(n)) / sum(interior_points(REF_GRID))
 
 
+def metric_name(args, n):
+    base = f"V-cycles/s at 513^3 fp64, linear V({args.pre},{args.post})"
+    if tuple(n) == REF_GRID:
+        return base
+    arr = "x".join(str(d + 2) for d in n)
+    kind = "weak scaling" if args.grid is None else "grid given by --grid"
+    return (f"513^3-equivalent V-cycles/s fp64, linear V({args.pre},{args.post}) ({kind}: {arr} arrays on {args.gpus} GPU(s), "
+            f"cycles/s x {work_ratio(n):.3f})")
+
+
 def workload_config(args):
     n = resolve_grid(args)
     arr = "x".join(str(d + 2) for d in n)
@@ -198,11 +290,141 @@ def workload_config(args):
                        f"fp64, omega 0.8",
            "grid": list(n), "mode": 0, "pre": args.pre, "post": args.post,
            "l2": "inputs larger than L2 (each level-0 array is %.2f GB)" % ((n[0] + 2) * (n[1] + 2) * (n[2] + 2) * 8 / 1e9),
-           "partition": "single GPU" if args.gpus == 1 else f"z-slabs over {args.gpus} GPUs, NCCL halo exchange, coarse levels replicated"}
+           "partition": "single GPU" if args.gpus == 1 else f"z-slabs over {args.gpus} GPUs, ghost planes over NVLink, coarse levels replicated"}
     if n != REF_GRID:
         cfg["value_normalisation"] = ("value = V-cycles/s on this grid x %.4f (its lattice points over all levels / those of the 513^3 "
                                       "grid): whole-job throughput in 513^3-equivalent V-cycles/s" % work_ratio(n))
     return cfg
+
+
+class Job:
+    """torch.distributed plumbing of one bench process"""
+
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+        self.gs = entry.load_package()
+        self.gs.load()  # raises if the CUDA library is missing: no fallback
+
+    def nccl_id(self):
+        if self.dist is None:
+            return None
+        box = [self.gs.comm_unique_id() if self.rank == 0 else None]
+        self.dist.broadcast_object_list(box, src=0)
+        return box[0]
+
+    def solver(self, n, mode=0, pre=2, post=2, slab=True):
+        p = self.gs.make_params(n, mode=mode, pre=pre, post=post, maxiter=1, tol=1e-30)
+        if slab and self.world > 1:
+            return self.gs.GpuSolve(p, device=self.local, rank=self.rank, world=self.world, nccl_id=self.nccl_id())
+        return self.gs.GpuSolve(p, device=self.local)
+
+    def barrier(self, *solvers):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+        for s in solvers:
+            s.synchronize()
+
+    def max_over_ranks(self, x):
+        if self.dist is None:
+            return x
+        t = self.torch.tensor([x], device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def time_cycles(self, solver, steps, warm, step=None):
+        """CUDA events on the library's stream around `steps` calls, barrier + synchronize on both sides, max over ranks;
+        returns (ms per step, last return value, kernels launched)"""
+        torch = self.torch
+        step = step or solver.vcycle
+        stream = torch.cuda.ExternalStream(solver.stream, device=torch.device("cuda", self.local))
+        for _ in range(warm):
+            step()
+        self.barrier(solver)
+        l0 = solver.launches
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        out = None
+        for _ in range(steps):
+            out = step()
+        ev1.record(stream)
+        self.barrier(solver)
+        return self.max_over_ranks(ev0.elapsed_time(ev1)) / steps, out, solver.launches - l0
+
+
+def per_level_profile(solver, reps):
+    """per-operator CUDA events (graph off): ({op: {ms_per_cycle, launches_per_cycle}}, [per level {op: launches}],
+    [per level {op: ms}], sweeps per cycle on level 0)"""
+    solver.set_option("timing", 1)
+    solver.reset_timing()
+    for _ in range(reps):
+        solver.vcycle()
+    allt = solver.timing()
+    nlev = solver.num_levels
+    ll, lm = [], []
+    for l in range(nlev):
+        t = solver.level_timing(l)
+        ll.append({k: v[1] / reps for k, v in t.items() if v[1]})
+        lm.append({k: v[0] / reps for k, v in t.items() if v[1]})
+    sweeps0 = solver.level_sweeps(0) / reps
+    solver.set_option("timing", 0)
+    per_op = {k: {"ms_per_cycle": v[0] / reps, "launches_per_cycle": v[1] / reps} for k, v in allt.items()}
+    return per_op, ll, lm, sweeps0
+
+
+def slab_parity(job, n=255, cycles=2):
+    """Before anything is timed: the slab solver must give the ONE-GPU fields bit for bit (Jacobi is order independent
+    and every rank runs the same kernels on its planes) and the norms to 1e-12 (only the summation tree differs) — all
+    three modes, with GPUSOLVE_SLAB_MIN_POINTS=0 so that several levels are partitioned and (world >= 3) there are ranks
+    with a neighbour on both sides.  Raises SystemExit on a mismatch."""
+    import numpy as np
+    gs = job.gs
+    old = os.environ.get("GPUSOLVE_SLAB_MIN_POINTS")
+    os.environ["GPUSOLVE_SLAB_MIN_POINTS"] = "0"
+    rec = {"grid": n, "cycles": cycles, "world": job.world, "modes": [], "bitwise": True, "max_norm_rel_diff": 0.0, "partitioned_levels": None}
+    try:
+        for mode in (0, 1, 2):
+            pre = 3 if mode == 2 else 2
+            slab = job.solver(n, mode=mode, pre=pre, post=pre)
+            p = gs.make_params(n, mode=mode, pre=pre, post=pre, maxiter=1, tol=1e-30)
+            rec["partitioned_levels"] = gs.partition(p, job.world, job.rank, 0)[2]
+            field = gs.NEWTONV if mode == 2 else gs.V
+            step = (lambda s: s.newton_step()[0]) if mode == 2 else (lambda s: s.vcycle())
+            norms = [step(slab) for _ in range(cycles)]
+            got = [slab.get(l, field if (mode == 2 and l == 0) else gs.V) for l in (0, 1)]   # collective
+            ok, nerr = True, 0.0
+            if job.rank == 0:
+                one = job.solver(n, mode=mode, pre=pre, post=pre, slab=False)
+                ref = [step(one) for _ in range(cycles)]
+                want = [one.get(l, field if (mode == 2 and l == 0) else gs.V) for l in (0, 1)]
+                ok = all(bool(np.array_equal(a, b)) for a, b in zip(got, want))
+                nerr = max(abs(a - b) / abs(b) for a, b in zip(norms, ref))
+                one.close()
+            slab.close()
+            bad = job.max_over_ranks(0.0 if (ok and nerr <= 1e-12) else 1.0)
+            rec["modes"].append(mode)
+            rec["bitwise"] = rec["bitwise"] and ok
+            rec["max_norm_rel_diff"] = max(rec["max_norm_rel_diff"], nerr)
+            if bad:
+                if job.rank == 0:
+                    sys.stderr.write(f"slab parity FAILED: mode {mode} world {job.world} n {n}: fields bitwise {ok}, norm rel diff {nerr:.3e}\n")
+                raise SystemExit(3)
+    finally:
+        if old is None:
+            os.environ.pop("GPUSOLVE_SLAB_MIN_POINTS", None)
+        else:
+            os.environ["GPUSOLVE_SLAB_MIN_POINTS"] = old
+    return rec
 
 
 def main():
@@ -217,6 +439,8 @@ def main():
     ap.add_argument("--post", type=int, default=2)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the modes / small / strong-scaling sub-records")
+    ap.add_argument("--no-parity", action="store_true", help="skip the slab-vs-one-GPU check at N > 1")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
 
@@ -233,79 +457,40 @@ def main():
         return run_reference_arm(args, emit)
 
     import numpy as np
-    import torch
-    gs = entry.load_package()
-    gs.load()  # raises if the CUDA library is missing: no fallback
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    job = Job()
+    gs, rank, world = job.gs, job.rank, job.world
     if args.gpus != world and world > 1:
         args.gpus = world
-    dist = None
-    torch.cuda.set_device(local_rank)
-    nccl_id = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        box = [gs.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        nccl_id = box[0]
+    peak, peak_src = measured_peaks()
+
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = slab_parity(job)
 
     n, pre, post = resolve_grid(args), args.pre, args.post
     wr = work_ratio(n)
-    p = gs.make_params(n, mode=0, pre=pre, post=post, maxiter=1, tol=1e-30)
-    solver = gs.GpuSolve(p, device=local_rank, rank=rank, world=world, nccl_id=nccl_id)
-    stream = torch.cuda.ExternalStream(solver.stream, device=torch.device("cuda", local_rank))
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-        solver.synchronize()
+    solver = job.solver(n, 0, pre, post)
 
     # ---- whole-job throughput: inputs resident in HBM ----
     for _ in range(args.warmup):
         solver.vcycle()
-    barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    l0 = solver.launches
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    job.barrier(solver)
+    sampler = ClockSampler(job.local) if rank == 0 else None
     t_wall0 = time.time()
-    ev0.record(stream)
-    norm = 0.0
-    for _ in range(args.steps):
-        norm = solver.vcycle()
-    ev1.record(stream)
-    barrier()
+    ms_per_step, norm, launches = job.time_cycles(solver, args.steps, 0)
     t_wall1 = time.time()
-    ms = ev0.elapsed_time(ev1)
-    launches = solver.launches - l0
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
-    if dist is not None:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    ms_per_step = ms / args.steps
     value = 1e3 / ms_per_step * wr
 
-    # ---- dominant kernel (fine-level smoother sweep) inside the V-cycle, per-operator CUDA events ----
-    solver.set_option("timing", 1)
-    solver.reset_timing()
+    # ---- dominant kernel (fine-level two-sweep smoother pass) inside the V-cycle, per-operator CUDA events ----
     reps = max(3, min(args.steps, 10))
-    for _ in range(reps):
-        solver.vcycle()
-    lt = solver.level_timing(0)
-    allt = solver.timing()
-    solver.set_option("timing", 0)
-    sm_ms, sm_n = lt["smooth"]
-    sweeps = solver.level_sweeps(0)          # Jacobi sweeps those launches applied (2 per launch of smooth2_tma)
+    per_op, ll, lm, sweeps0 = per_level_profile(solver, reps)
     P = interior_points(n)
-    per_launch = sweeps / max(sm_n, 1)
-    launch_ms = sm_ms / max(sm_n, 1)
-    launch_bytes = 24.0 * P[0] / world * per_launch      # 24 B per lattice update
-    peak, peak_src = measured_peaks()
-    achieved = launch_bytes / (launch_ms * 1e-3) / 1e9
+    sm_n = ll[0].get("smooth", 0.0)
+    launch_ms = lm[0].get("smooth", 0.0) / max(sm_n, 1e-9)
+    per_launch = sweeps0 / max(sm_n, 1e-9)
+    pass_bytes = 24.0 * P[0] / world                      # read v, read f, write v'' once per launch (this rank's slab)
+    achieved = pass_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath) and n == REF_GRID:
@@ -315,19 +500,22 @@ def main():
              else "stencil_tma: one damped-Jacobi sweep per pass")
     roofline = {"bound": "hbm", "kernel": "fine-level smoother (level 0, inside the V-cycle) - " + kname, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": launch_bytes, "ms_per_launch": launch_ms, "sweeps_per_launch": per_launch,
-                "glups": sweeps * P[0] / (sm_ms * 1e-3) / 1e9,
+                "algorithmic_bytes_per_launch": pass_bytes, "ms_per_launch": launch_ms, "sweeps_per_launch": per_launch,
+                "glups": sweeps0 * P[0] / max(lm[0].get("smooth", 0.0) * 1e-3, 1e-12) / 1e9,
+                "lup_equivalent_gbs": 24.0 * P[0] / world * per_launch / (launch_ms * 1e-3) / 1e9,
                 "dram_gbs": (traffic / (launch_ms * 1e-3) / 1e9) if traffic else None,
-                "note": "achieved = algorithmic bytes (24 B per lattice update x updates per launch) / launch time; a temporally blocked "
-                        "launch does two updates per point for one pass over v and f, so achieved may exceed the copy peak while the DRAM "
-                        "traffic (ncu, `traffic`) stays at ~25 B per point"}
+                "dram_frac": (traffic / (launch_ms * 1e-3) / 1e9 / peak) if traffic else None,
+                "note": "achieved = compulsory bytes of ONE PASS (v and f read, v'' written once: 24 B per point of this GPU's slab) / "
+                        "average launch time, CUDA events inside the V-cycle; frac is a bandwidth fraction.  The pass applies "
+                        "sweeps_per_launch Jacobi sweeps: glups and lup_equivalent_gbs (24 B per lattice UPDATE, SURVEY 8d) carry that"}
     vbytes = vcycle_algorithmic_bytes(n, pre, post)
-    per_op = {k: {"ms_per_cycle": v[0] / reps, "launches_per_cycle": v[1] / reps} for k, v in allt.items()}
+    launched_bytes = pass_level_bytes(n, 0, ll)
 
     # ---- end to end through the C ABI with HOST buffers: H2D of the step's right-hand side from pinned
     #      memory (gs_set_field), the V-cycle, D2H of the step's residual norm ----
     e2e = None
     if not args.no_e2e:
+        torch = job.torch
         shape = solver.shape(0)
         f_host = torch.empty(shape, dtype=torch.float64).pin_memory()
         f_np = f_host.numpy()
@@ -336,44 +524,142 @@ def main():
         for _ in range(2):
             solver.set(0, gs.F, f_np)
             solver.vcycle()
-        barrier()
+        job.barrier(solver)
         t0 = time.perf_counter()
         for _ in range(k):
             solver.set(0, gs.F, f_np)      # host -> device, inside the timed region
             norm = solver.vcycle()         # device -> host: the cycle's residual norm
-        barrier()
-        dt = time.perf_counter() - t0
-        if dist is not None:
-            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
-        e2e = {"value": k / dt * wr, "unit": "V-cycles/s", "h2d_bytes_per_step": int(np.prod(shape)) * 8 // 1, "d2h_bytes_per_step": 8,
-               "steps": k, "note": "gs_set_field(F) from pinned host memory + gs_vcycle + norm read-back per step"}
+        job.barrier(solver)
+        dt = job.max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": k / dt * wr, "unit": "V-cycles/s", "h2d_bytes_per_step": int(np.prod(shape)) * 8, "d2h_bytes_per_step": 8,
+               "steps": k, "ms_per_step": 1e3 * dt / k,
+               "note": "gs_set_field(F) from pinned host memory + gs_vcycle + norm read-back per step; the result read back is the "
+                       "8-byte residual norm (the reference's solve contract), never the field"}
         del f_host
+    solver.close()
+
+    extras = {}
+    if not args.no_extras:
+        # ---- strong scaling on 1023^3 (BASELINE.json configs[4]) ----
+        big = (1023, 1023, 1023)
+        t1 = None
+        if rank == 0:
+            one = job.solver(big, 0, 2, 2, slab=False)
+            for _ in range(3):
+                one.vcycle()
+            one.synchronize()
+            torch = job.torch
+            st = torch.cuda.ExternalStream(one.stream, device=torch.device("cuda", job.local))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for _ in range(10):
+                one.vcycle()
+            e1.record(st)
+            one.synchronize()
+            t1 = e0.elapsed_time(e1) / 10
+            one.close()
+        if world == 1:
+            extras["strong_ref_1023"] = {"ms_per_cycle": t1, "grid": list(big), "cycles": 10, "note": "1023^3 (1025^3 arrays) on this one GPU"}
+        else:
+            t1 = job.max_over_ranks(t1 if t1 is not None else 0.0)
+            s = job.solver(big, 0, 2, 2)
+            tn, _, _ = job.time_cycles(s, 10, 3)
+            s.close()
+            extras["strong_1023"] = {"ms_per_cycle": tn, "ms_per_cycle_1gpu": t1, "efficiency": t1 / (world * tn), "speedup": t1 / tn,
+                                     "grid": list(big), "cycles": 10,
+                                     "note": "same 1023^3 grid on N GPUs vs on GPU 0 alone in this run (CUDA events, max over ranks)"}
+        # ---- BASELINE.json configs[2], [3] at 513^3 and the shipped config at 129^3, one GPU ----
+        if world == 1:
+            extras["modes"] = {}
+            for mode, (mpre, mpost) in ((1, (2, 2)), (2, (3, 3))):
+                s = job.solver(REF_GRID, mode, mpre, mpost)
+                if mode == 2:
+                    s.newton_step()      # a realistic Newton iterate on every level
+                ms, _, ml = job.time_cycles(s, 10, 3)
+                pop, mll, mlm, msw = per_level_profile(s, 5)
+                s.close()
+                sweep = 32 if mode == 2 else 24
+                spn = mll[0].get("smooth", 0.0)
+                sp_ms = mlm[0].get("smooth", 0.0) / max(spn, 1e-9)
+                lb = pass_level_bytes(REF_GRID, mode, mll)
+                extras["modes"][str(mode)] = {
+                    "config": f"mode {mode} ({'FAS, gamma=1' if mode == 1 else 'Newton-linearised, precomputed coefficient'}), 513^3, V({mpre},{mpost})",
+                    "ms_per_cycle": ms, "vcycles_per_s": 1e3 / ms, "launches_per_cycle": ml / 10,
+                    "dominant_kernel": "smooth2u_tma<%s> level 0" % ("KM_NONLINEAR" if mode == 1 else "KM_NEWTON_COEF"),
+                    "pass_ms": sp_ms, "pass_bytes": sweep * P[0], "pass_frac_of_hbm_peak": sweep * P[0] / (sp_ms * 1e-3) / 1e9 / peak,
+                    "sweeps_per_pass": msw / max(spn, 1e-9), "glups": msw * P[0] / max(mlm[0].get("smooth", 1e-9) * 1e-3, 1e-12) / 1e9,
+                    "vcycle_pass_level_bytes": lb, "vcycle_frac_of_peak": lb / (ms * 1e-3) / 1e9 / peak, "per_operator": pop,
+                    "binds": ("fp64 pipe (exp + divide per point per sweep; ncu: profiles/r02_ncu_modes_summary.txt)" if mode == 1 else
+                              "HBM and fp64 pipe together (divide per point per sweep, 32 B per point; ncu: profiles/r02_ncu_modes_summary.txt)")}
+            # the shipped examples/data-2nd_order.conf (BASELINE configs[0]): Newton, 127^3, V(3,3) — ms per Newton iteration
+            p = gs.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5)
+            s = gs.GpuSolve(p, device=job.local)
+            s.newton_step()
+            s.synchronize()
+            t0 = time.perf_counter()
+            inner = 0
+            for _ in range(3):
+                inner += s.newton_step()[1]
+            s.synchronize()
+            gpu_ms = (time.perf_counter() - t0) / 3 * 1e3
+            s.close()
+            small = {"n": 127, "mode": 2, "pre": 3, "post": 3, "ms_per_newton_iter": gpu_ms, "inner_cycles_per_iter": inner / 3,
+                     "note": "examples/data-2nd_order.conf as shipped; wall clock over 3 Newton iterations after one warm-up (includes the host's "
+                             "norm read-backs)"}
+            if not args.no_cpu:
+                orc, kind = cpu_oracle()
+                o = orc.Oracle(orc.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5), kind)
+                o.set_threads(os.cpu_count())
+                o.newton_begin()
+                import numpy as _np
+
+                def cpu_step():
+                    o.newton_compF()
+                    o.set(0, orc.V, _np.zeros(o.shape(0)))
+                    c = o.newton_find_error()
+                    o.newton_compF()
+                    return c
+                cpu_step()
+                t0 = time.perf_counter()
+                cin = sum(cpu_step() for _ in range(3))
+                small["cpu_ms_per_newton_iter"] = (time.perf_counter() - t0) / 3 * 1e3
+                small["cpu_inner_cycles_per_iter"] = cin / 3
+                small["cpu_kind"], small["cpu_cores"] = kind, os.cpu_count()
+                o.close()
+            extras["small"] = small
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, kind, cores, sample = run_cpu(n, pre, post, 1, 0, budget_s=30.0)
-        cpu = {"value": v * wr, "unit": "V-cycles/s", "cores": cores, "kind": kind, "sample": sample}
+        r = run_cpu(n, pre, post, 3, 1, budget_s=30.0)
+        cpu = {"value": r["cycles_per_s"] * wr, "unit": "V-cycles/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
+               "extrapolated": r["extrapolated"]}
 
     if rank == 0:
         line = {
-            "metric": "V-cycles/s at 513^3 fp64, linear V(2,2)" if (pre, post) == (2, 2) else f"V-cycles/s at 513^3 fp64, linear V({pre},{post})",
+            "metric": metric_name(args, n),
             "value": value, "unit": "V-cycles/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if args.grid is None else "strong",
             "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (analytic RHS, src/cpu/CpuGridData.cpp:47-58)", "config": workload_config(args),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "vcycle": {"algorithmic_bytes": vbytes, "achieved_gbs": vbytes / (ms_per_step * 1e-3) / 1e9,
-                       "frac_of_peak": vbytes / (ms_per_step * 1e-3) / 1e9 / peak, "per_operator": per_op,
-                       "glups_smoother_equivalent": (pre + post) * sum(P) / (ms_per_step * 1e-3) / 1e9},
+            "vcycle": {"algorithmic_bytes": vbytes, "pass_level_bytes": launched_bytes,
+                       "achieved_gbs_per_gpu": launched_bytes / world / (ms_per_step * 1e-3) / 1e9,
+                       "frac_of_peak": launched_bytes / world / (ms_per_step * 1e-3) / 1e9 / peak,
+                       "survey_bound_gbs_per_gpu": vbytes / world / (ms_per_step * 1e-3) / 1e9,
+                       "per_operator": per_op, "per_level_ms": lm,
+                       "glups_smoother_equivalent": (pre + post) * sum(P) / (ms_per_step * 1e-3) / 1e9,
+                       "note": "pass_level_bytes = compulsory traffic of the passes launched per cycle (a two-sweep pass counts once); "
+                               "frac_of_peak = that / world / time / peak, i.e. per GPU; algorithmic_bytes is SURVEY 8d's B_V (one pass per "
+                               "reference operator)"},
             "final_residual_norm": norm, "vcycles_per_s_on_this_grid": 1e3 / ms_per_step, "work_ratio_vs_513": wr,
         }
+        if parity is not None:
+            line["slab_parity"] = parity
+        line.update(extras)
         emit(line)
-    solver.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    if job.dist is not None:
+        job.dist.barrier()
+        job.dist.destroy_process_group()
     return 0
 
 

@@ -22,6 +22,7 @@
 
 int gs_pick_zchunk_waves(const LaunchCtx& cx, int tiles, int planes, int ctas_per_sm, int overhead, int min_chunk, int max_chunk,
                          bool even);
+void gs_tensor_map_drop(const void* base);
 
 // ---------------------------------------------------------------------------------
 // errors
@@ -705,32 +706,31 @@ int enqueue_vcycle(gs_handle* h)
     return rc;
 }
 
+// Key of a captured V-cycle: only the state that changes BETWEEN cycles of one handle — which of the two buffers is `v` on
+// each level, whether level 0 already holds pre-smoothing sweeps from the fused norm pass, and (slabs) which ghost planes
+// are current, which decides the exchanges the captured cycle contains.  Everything else a capture bakes in (kernel
+// variants, tuning, options) is covered by drop_graphs(): gs_set_option destroys the cache, so an option changed after
+// the first gs_vcycle can never replay a stale configuration.
 uint64_t parity_key(const gs_handle* h)
 {
-    // which of the two buffers is `v` on each level, plus everything else a captured graph bakes in
-    uint64_t key = 0;
-    for (size_t l = 0; l < h->lev.size(); l++)
-        if (h->lev[l].v > h->lev[l].vtmp) key |= 1ull << l;
-    key |= (uint64_t)h->opt_kernels << 40;
-    key |= (uint64_t)(h->cx.tune.smooth_variant & 0x3f) << 32;
-    key ^= (uint64_t)(h->cx.tune.zchunk & 0xfff) << 20;
-    key ^= (uint64_t)(h->cx.tune.rr_variant & 3) << 18;
-    key ^= (uint64_t)(h->lev[0].pre_valid & 3) << 15;
-    key ^= (uint64_t)(h->cx.tune.fuse2 & 7) << 12;
-    key ^= (uint64_t)(h->opt_fuse_norm ? 1 : 0) << 17;
-    key ^= (uint64_t)(h->lev[0].ar & 3) << 10;
-    key ^= (uint64_t)(h->lev[0].ar & 4) << 4;
-    key ^= (uint64_t)(h->cx.tune.wave & 1) << 9;
-    key ^= (uint64_t)(h->opt_vzero & 1) << 8;
-    key ^= (uint64_t)(tail_first_level(h) + 1) * 0xD6E8FEB86659FD93ull;
-    key ^= (uint64_t)(h->opt_overlap & 1) << 7;
-    key |= (uint64_t)(h->p.pre & 0xff) << 44;
-    key |= (uint64_t)(h->p.post & 0xff) << 52;
-    // slabs: which ghost planes are current decides which exchanges the captured cycle contains
-    uint64_t gvs = 0;
-    for (size_t l = 0; l < h->lev.size(); l++) gvs = gvs * 3 + (uint64_t)(partitioned(h, (int)l) ? h->lev[l].gv : 0);
-    key ^= gvs * 0x9E3779B97F4A7C15ull;
+    uint64_t key = 0xcbf29ce484222325ull;
+    auto mix = [&](uint64_t v) { key = (key ^ v) * 0x100000001b3ull; };
+    for (size_t l = 0; l < h->lev.size(); l++) {
+        const Level& L = h->lev[l];
+        mix((L.v > L.vtmp ? 1u : 0u) | (uint64_t)(partitioned(h, (int)l) ? L.gv : 0) << 1 | (uint64_t)(L.vzero_next ? 1 : 0) << 3);
+    }
+    mix((uint64_t)h->lev[0].pre_valid);
     return key;
+}
+
+void drop_graphs(gs_handle* h)
+{
+    for (auto& kv : h->graphs) cudaGraphExecDestroy(kv.second);
+    h->graphs.clear();
+    h->graphs_launches.clear();
+    h->graphs_pre_valid.clear();
+    h->graphs_gv.clear();
+    h->graphs_swapped.clear();
 }
 
 int run_vcycle(gs_handle* h, double* norm)
@@ -1244,10 +1244,13 @@ int gs_destroy(gs_handle* h)
     if (!h) return GS_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    for (auto& kv : h->graphs) cudaGraphExecDestroy(kv.second);
+    drop_graphs(h);
     for (auto& L : h->lev)
         for (double* a : {L.v, L.vtmp, L.f, L.r, L.restV, L.newtonV, L.coef})
-            if (a) cudaFree(a);
+            if (a) {
+                gs_tensor_map_drop(a);  // the address may come back from a later cudaMalloc with another geometry
+                cudaFree(a);
+            }
     if (h->newtonF) cudaFree(h->newtonF);
     if (h->stage) cudaFree(h->stage);
     if (h->cx.norm.partials) cudaFree(h->cx.norm.partials);
@@ -1629,6 +1632,9 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
 {
     if (!h || !name) return fail(GS_EINVAL, "null argument");
     std::string n(name);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    drop_graphs(h);  // a captured V-cycle bakes in every option: never replay one captured under other settings
     if (n == "kernels") {
         h->opt_kernels = value != 0;
         for (auto& L : h->lev) L.coef_valid = false;

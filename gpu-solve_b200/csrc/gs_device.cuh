@@ -8,7 +8,45 @@
 #pragma once
 #include <cuda.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "gs_internal.h"
+
+// ---- per-device one-time kernel setup ----
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) and the occupancy of a kernel belong to a DEVICE, and the C ABI takes
+// a device per handle: every launcher keeps its "prepared" flag and occupancy per device (slot = cudaGetDevice()).
+constexpr int GS_MAX_DEVICES = 64;
+struct DevOnce {
+    std::atomic<int> v[GS_MAX_DEVICES];  // 0 = not set up on that device yet, else the value setup() reported (>= 1)
+};
+inline int gs_cur_device()
+{
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= GS_MAX_DEVICES) d = 0;
+    return d;
+}
+// runs setup(int* value) once per device (thread safe); *value_out = what it reported for the current device
+template <class Setup>
+inline cudaError_t gs_dev_once(DevOnce& st, int* value_out, Setup&& setup)
+{
+    static std::mutex mu;
+    const int d = gs_cur_device();
+    int o = st.v[d].load(std::memory_order_acquire);
+    if (o == 0) {
+        std::lock_guard<std::mutex> lock(mu);
+        o = st.v[d].load(std::memory_order_acquire);
+        if (o == 0) {
+            int q = 1;
+            const cudaError_t e = setup(&q);
+            if (e != cudaSuccess) return e;
+            o = q > 0 ? q : 1;
+            st.v[d].store(o, std::memory_order_release);
+        }
+    }
+    if (value_out) *value_out = o;
+    return cudaSuccess;
+}
 
 // ---- host helpers shared by the tuned translation units (kernels_fast.cu) ----
 // TMA descriptor of a level array viewed as [nzl][Y][pitch] doubles with a bw x bh x 1 box (cached)

@@ -13,6 +13,7 @@
 #include <stdint.h>
 
 #include "../../include/gpusolve_cuda.h"
+#include "../../include/gpusolve_cuda_tuning.h"
 
 #define GS_XOFF 15  // doubles in front of logical x = 0, so that x = 1 sits at element 16
 

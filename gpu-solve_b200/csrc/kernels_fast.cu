@@ -40,13 +40,16 @@ static EncodeTiledFn encode_fn()
     return fn;
 }
 
-// one descriptor per (array, geometry, box); arrays live as long as the handle, so cache them
+// one descriptor per (array, geometry, box); arrays live as long as the handle, so cache them (gs_destroy drops them)
+typedef std::tuple<const void*, i64, int, int, int, int> TmKey;
+static std::map<TmKey, CUtensorMap> g_tm_cache;
+static std::mutex g_tm_mu;
+
 bool gs_tensor_map(const double* base, const Geom& g, int bw, int bh, CUtensorMap* out)
 {
-    typedef std::tuple<const void*, i64, int, int, int, int> Key;
-    static std::map<Key, CUtensorMap> cache;
-    static std::mutex mu;
-    std::lock_guard<std::mutex> lock(mu);
+    typedef TmKey Key;
+    std::map<Key, CUtensorMap>& cache = g_tm_cache;
+    std::lock_guard<std::mutex> lock(g_tm_mu);
     Key key(base, g.pitch, g.Y, g.nzl, bw, bh);
     auto it = cache.find(key);
     if (it != cache.end()) {
@@ -67,6 +70,17 @@ bool gs_tensor_map(const double* base, const Geom& g, int bw, int bh, CUtensorMa
     cache[key] = m;
     *out = m;
     return true;
+}
+
+// forget the descriptors of an array that is about to be freed (gs_destroy): a later allocation may reuse the address
+void gs_tensor_map_drop(const void* base)
+{
+    if (!base) return;
+    std::lock_guard<std::mutex> lock(g_tm_mu);
+    for (auto it = g_tm_cache.begin(); it != g_tm_cache.end();) {
+        if (std::get<0>(it->first) == base) it = g_tm_cache.erase(it);
+        else ++it;
+    }
 }
 
 // planes per CTA: as long as tune.zchunk allows (each chunk re-reads two planes), but short
@@ -294,16 +308,18 @@ template <int KM, int AR, int OP, int TX, int TY, int NSTAGE>
 cudaError_t launch_tma(const LaunchCtx& cx, FastP p, bool* handled)
 {
     using Cfg = TmaCfg<TX, TY, NSTAGE>;
-    static bool prepared = false;  // raise the dynamic shared memory limit once per instantiation (outside stream capture:
-    static int occ = 1;            // kf_prepare() instantiates every kernel the dispatchers can reach)
-    if (!prepared) {
+    // raise the dynamic shared memory limit once per instantiation and device (outside stream capture: kf_prepare()
+    // instantiates every kernel the dispatchers can reach)
+    static DevOnce once;
+    int occ = 1;
+    cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
         cudaError_t e = cudaFuncSetAttribute(stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
-        if (e != cudaSuccess) return e;
-        prepared = true;
-    }
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
+        return e;
+    });
+    if (pe != cudaSuccess) return pe;
     if (!p.vin) return cudaSuccess;  // preparation call
     CUtensorMap mv, mf;
     if (!gs_tensor_map(p.vin, p.g, Cfg::VW, Cfg::VH, &mv) || !gs_tensor_map(p.f, p.g, TX, TY, &mf)) return cudaSuccess;  // not handled
@@ -434,12 +450,10 @@ cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, i
     return e;
 }
 
-// one-time per-process setup: every launcher raises its kernel's dynamic shared memory limit on a
+// one-time per-device setup: every launcher raises its kernel's dynamic shared memory limit on a
 // null-pointer call, so that nothing but launches happens later under stream capture
 cudaError_t kf_prepare()
 {
-    static bool done = false;
-    if (done) return cudaSuccess;
     LaunchCtx cx{};
     Geom g{};
     PointK k{};
@@ -459,6 +473,5 @@ cudaError_t kf_prepare()
             }
             g.nx = 0;
         }
-    done = e == cudaSuccess;
     return e;
 }

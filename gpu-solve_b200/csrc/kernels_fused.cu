@@ -435,16 +435,16 @@ template <int KM, int AR, bool NORM, int TY, int NSTAGE>
 cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
 {
     using Cfg = S2Cfg<TY, NSTAGE>;
-    static bool prepared = false;
-    static int occ = 1;
-    if (!prepared) {
+    static DevOnce once;
+    int occ = 1;
+    cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
         cudaError_t e = cudaFuncSetAttribute(smooth2_tma<KM, AR, NORM, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smooth2_tma<KM, AR, NORM, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
-        if (e != cudaSuccess) return e;
-        prepared = true;
-    }
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, smooth2_tma<KM, AR, NORM, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
+        return e;
+    });
+    if (pe != cudaSuccess) return pe;
     if (!p.vin) return cudaSuccess;  // preparation call
     CUtensorMap mv, mf;
     if (!gs_tensor_map(p.vin, p.g, Cfg::BW, Cfg::VH, &mv) || !gs_tensor_map(p.f, p.g, Cfg::BW, Cfg::FH, &mf)) return cudaSuccess;
@@ -469,14 +469,14 @@ template <int KM, int AR, bool NORM, int TY, bool VZ>
 cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
 {
     using Cfg = S2uCfg<TY>;
-    static bool prepared = false;
-    static int occ = 1;
-    if (!prepared) {
+    static DevOnce once;
+    int occ = 1;
+    cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
         cudaError_t e = cudaFuncSetAttribute(smooth2u_tma<KM, AR, NORM, TY, VZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smooth2u_tma<KM, AR, NORM, TY, VZ>, Cfg::THREADS, Cfg::SMEM);
-        if (e != cudaSuccess) return e;
-        prepared = true;
-    }
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, smooth2u_tma<KM, AR, NORM, TY, VZ>, Cfg::THREADS, Cfg::SMEM);
+        return e;
+    });
+    if (pe != cudaSuccess) return pe;
     if (!p.vin) return cudaSuccess;  // preparation call
     CUtensorMap mv, mf;
     if (!gs_tensor_map(p.f, p.g, Cfg::BW, Cfg::FH, &mf)) return cudaSuccess;
@@ -547,8 +547,6 @@ cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int z
 
 cudaError_t kx_prepare()
 {
-    static bool done = false;
-    if (done) return cudaSuccess;
     LaunchCtx cx{};
     Geom g{};
     PointK k{};
@@ -559,6 +557,5 @@ cudaError_t kx_prepare()
             for (int nm = 0; nm < 2 && e == cudaSuccess; nm++)
                 for (int vz = 0; vz < 2 && e == cudaSuccess; vz++)
                     e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, vz != 0, &handled);
-    done = e == cudaSuccess;
     return e;
 }

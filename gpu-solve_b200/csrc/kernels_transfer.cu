@@ -49,7 +49,8 @@ __device__ __forceinline__ Ay4 load_ay(const double* __restrict__ cv, i64 b, i64
 }
 
 constexpr int PBX = 32, PBY = 8;
-int g_prolong_occ = 8;  // resident CTAs per SM of prolong_correct_zmarch (kt_prepare)
+DevOnce g_prolong_once;  // resident CTAs per SM of prolong_correct_zmarch, per device
+cudaError_t prolong_occ(int* occ);
 
 __global__ void __launch_bounds__(PBX* PBY) prolong_correct_zmarch(ProlongFastP p)
 {
@@ -113,6 +114,12 @@ __global__ void __launch_bounds__(PBX* PBY) prolong_correct_zmarch(ProlongFastP 
         put(c, v00, v01, e0);
         if (two) put(c + plane, v10, v11, e1);
     }
+}
+
+cudaError_t prolong_occ(int* occ)
+{
+    return gs_dev_once(g_prolong_once, occ,
+                       [](int* o) { return cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, prolong_correct_zmarch, PBX * PBY, 0); });
 }
 
 // ---------------------------------------------------------------------------------
@@ -453,7 +460,9 @@ cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
     const int npx = (gf.nx + 1) / 2, npy = (gf.ny + 1) / 2;
     ProlongFastP p{gf, gc, zb, ze, 0, vin, vout, coarse};
     const int tiles = ((npx + PBX - 1) / PBX) * ((npy + PBY - 1) / PBY);
-    if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tiles, ze - zb, g_prolong_occ, 2, 8, 128, true);
+    int occ = 8;
+    if (cudaError_t e = prolong_occ(&occ)) return e;
+    if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tiles, ze - zb, occ, 2, 8, 128, true);
     else p.zchunk = gs_pick_zchunk(cx, tiles, ze - zb, 64);
     p.zchunk += p.zchunk & 1;  // even chunks: every chunk starts on the same plane parity
     dim3 grid((npx + PBX - 1) / PBX, (npy + PBY - 1) / PBY, (ze - zb + p.zchunk - 1) / p.zchunk);
@@ -469,16 +478,16 @@ template <int KM, int AR, int CX, int CY, int NSTAGE, bool SP>
 cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 {
     using Cfg = RRCfg<CX, CY, NSTAGE, SP>;
-    static bool prepared = false;
-    static int occ = 1;
-    if (!prepared) {
+    static DevOnce once;
+    int occ = 1;
+    cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
         cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, AR, CX, CY, NSTAGE, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, resid_restrict_tma<KM, AR, CX, CY, NSTAGE, SP>, Cfg::THREADS, Cfg::SMEM);
-        if (e != cudaSuccess) return e;
-        prepared = true;
-    }
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, resid_restrict_tma<KM, AR, CX, CY, NSTAGE, SP>, Cfg::THREADS, Cfg::SMEM);
+        return e;
+    });
+    if (pe != cudaSuccess) return pe;
     if (!p.v) return cudaSuccess;  // preparation call
     CUtensorMap mv;
     if (!gs_tensor_map(p.v, p.gf, Cfg::VW, Cfg::VH, &mv)) return cudaSuccess;  // not handled
@@ -532,8 +541,6 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& g
 
 cudaError_t kt_prepare()
 {
-    static bool done = false;
-    if (done) return cudaSuccess;
     LaunchCtx cx{};
     Geom g{};
     PointK k{};
@@ -542,7 +549,7 @@ cudaError_t kt_prepare()
     for (int km = 0; km < 4 && e == cudaSuccess; km++)
         for (int pw = 0; pw < 8 && e == cudaSuccess; pw++)
             e = kt_resid_restrict(cx, km, pw, g, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_prolong_occ, prolong_correct_zmarch, PBX * PBY, 0);
-    done = e == cudaSuccess;
+    int occ;
+    if (e == cudaSuccess) e = prolong_occ(&occ);
     return e;
 }

@@ -123,17 +123,6 @@ int  gs_destroy(gs_handle* h);
 int  gs_partition(const gs_params* p, int world, int rank, int level,
                   uint64_t* z_begin, uint64_t* z_end, int* replicated_from);
 
-/* z-chunk length the z-marching kernels use for `planes` planes of a level cut into `tiles` xy tiles, pure host
- * arithmetic (no GPU): the chunk count that minimises (waves of sm_count * ctas_per_sm resident CTAs) x (chunk +
- * overhead planes), so grids fill whole waves.  Introspection for tests and tuning; returns the chunk (>= 1). */
-int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int overhead,
-                    int min_chunk, int max_chunk, int even);
-
-/* first level of the coarse tail for option "tail_points" = tail_points (levels of at most that many interior points
- * run as one single-CTA kernel per V-cycle), pure host arithmetic: -1 = no tail (off, or only the coarsest level fits);
- * a negative GS_E* code below -1 never occurs for valid params */
-int  gs_plan_tail(const gs_params* p, int64_t tail_points);
-
 /* ---- introspection: CpuGridData::numLevels / getLevel (src/cpu/CpuGridData.h:22-33) */
 int  gs_num_levels(const gs_handle* h);
 int  gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hval);
@@ -191,22 +180,13 @@ int  gs_get_level_timing(gs_handle* h, int level, double ms[GS_OP_COUNT], uint64
 int  gs_get_level_sweeps(gs_handle* h, int level, uint64_t* sweeps);
 /* total kernels launched by this handle since creation */
 uint64_t gs_launch_count(const gs_handle* h);
-/* options: "kernels" = 0 simple one-thread-per-point kernels, 1 tuned (default);
+/* options a caller of the backend may want (all also settable as GPUSOLVE_<NAME> in the environment):
+ *          "kernels" = 0 general one-thread-per-point kernels, 1 tuned sm_100a kernels (default);
  *          "graph"   = 0/1 capture the V-cycle in a CUDA graph (default 1);
- *          "timing"  = 0/1 per-operator CUDA events (default 0, disables graph);
- *          "smooth_variant", "zchunk", "fast_min_n", "rr_variant" = kernel tuning knobs
- *          (gpu-solve_b200/csrc/kernels_fast.cu, kernels_transfer.cu);
- *          "fuse2" = 0 one Jacobi sweep per pass, 1..3 two sweeps per pass (tile variant,
- *          kernels_fused.cu; default 1), "fuse2_min_n", "zchunk2" its knobs;
- *          "fuse_norm" = 0/1 produce the next pre-smoothing sweep(s) together with the
- *          V-cycle's final residual norm (default 1);
- *          "unit_taps", "rcp_div", "wave", "vzero" = 0/1 same bits, slower (A/B switches, default 1);
- *          "timers" = 0/1 partial-timer lines in the reference Timer's format after a solve;
- *          "tail_points" = N > 0: levels of at most N interior points run as one single-CTA
- *          kernel per V-cycle (kernels_simple.cu ks_tail_*; default 0 = off);
- *          "overlap" = 0/1 slabs: refresh the ghost planes on a second stream while the operator that
- *          needs them runs on the planes that read no ghost (default 0);
- *          also GPUSOLVE_* environment */
+ *          "timing"  = 0/1 per-operator CUDA events (default 0; disables the graph);
+ *          "timers"  = 0/1 partial-timer tail in the reference Timer's format after each cycle of a solve.
+ * Kernel tuning knobs and A/B switches go through the same call but are not part of the backend contract:
+ * they are listed in gpusolve_cuda_tuning.h. */
 int  gs_set_option(gs_handle* h, const char* name, int64_t value);
 /* the CUDA stream all work of this handle is issued on (a cudaStream_t) */
 void* gs_stream(gs_handle* h);

@@ -113,3 +113,25 @@ def operator_script(b, mode):
         out["compF_norm"] = b.newton_compF()
         out["compF_f0"] = b.get(0, F)
     return out
+
+
+def full_size_script(b, mode, cycles, exact=None):
+    """The V-cycle path of one mode on the analytic right-hand side, as CpuSolver::solve / NewtonSolver::findError drive
+    it.  Modes 0/1: `cycles` V-cycles from v = 0.  Mode 2: a seeded Newton iterate on level 0, restricted down the
+    hierarchy (src/cpu/NewtonSolver.cpp:88-92), F(newtonV) (:48-81), then `cycles` V-cycles of the linearised
+    problem from v = 0 (:94-100).  Returns (norms, solution field id); with `exact` (a list) the oracle's compensated
+    norm of the field each returned norm was reduced from is appended to it."""
+    norms = []
+    if mode == 2:
+        b.set_newton_f(b.get(0, F))                       # NewtonSolver.cpp:12, newtonF = f_0
+        b.set(0, NEWTONV, seeded_field(b.shape(0), 3))
+        for l in range(b.num_levels - 2):                 # :88-92 (not onto the coarsest level)
+            b.restrict(l, NEWTONV, NEWTONV)
+        norms.append(b.newton_compF())
+        if exact is not None:
+            exact.append(b.norm_exact(0, F))
+    for _ in range(cycles):
+        norms.append(b.vcycle())
+        if exact is not None:
+            exact.append(b.norm_exact(0, R))
+    return norms, V

@@ -54,6 +54,16 @@ BIG_CASES = {
     "nt_wide_v24": dict(n=(100, 90, 47), mode=2, pre=2, post=4, maxiter=2, tol=1e-30),
 }
 
+# BASELINE.json configs[1]-[3] at their full size (arrays 513^3): one script per mode (backends.full_size_script), run
+# by the reference here (tests/golden/make_golden.py -> norms, digest, strided sample of the field) and by the C port
+# next to the GPU in the -m gpu suite (full-field comparison)
+FULL_CASES = {
+    "full511_lin_v22": dict(n=511, mode=0, pre=2, post=2, maxiter=2, tol=1e-30),
+    "full511_nl_v22": dict(n=511, mode=1, pre=2, post=2, maxiter=1, tol=1e-30),
+    "full511_nt_v33": dict(n=511, mode=2, pre=3, post=3, maxiter=1, tol=1e-30),
+}
+FULL_SAMPLE_STRIDE = 16  # field[::16, ::16, ::16] of the 513^3 result goes into fields.npz (33^3 values)
+
 OPERATOR_CASES = {
     "op_lin17": dict(n=17, mode=0),
     "op_lin_ragged": dict(n=(10, 7, 13), mode=0),

@@ -16,8 +16,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
-from backends import OracleBackend, operator_script, V, F, R, NEWTONV  # noqa: E402
-from cases import BIG_CASES, OPERATOR_CASES, SOLVE_CASES, digest  # noqa: E402
+from backends import OracleBackend, full_size_script, operator_script, V, F, R, NEWTONV  # noqa: E402
+from cases import BIG_CASES, FULL_CASES, FULL_SAMPLE_STRIDE, OPERATOR_CASES, SOLVE_CASES, digest  # noqa: E402
 
 KIND = "reference"
 
@@ -65,7 +65,37 @@ def operator_case(name, kw, arrays):
     return rec
 
 
+def full_case(name, kw, arrays):
+    """BASELINE configs[1]-[3] at 513^3: norms, compensated norm of the last residual, digest and a strided sample"""
+    b = OracleBackend(KIND, **kw)
+    b.set_threads(os.cpu_count())
+    norms, fid = full_size_script(b, kw["mode"], kw["maxiter"])
+    sol = b.get(0, fid)
+    rec = {"kwargs": {k: (list(v) if isinstance(v, tuple) else v) for k, v in kw.items()},
+           "norms": [x.hex() for x in norms], "norms_repr": [repr(x) for x in norms],
+           "norm_exact_final": b.norm_exact(0, R).hex(), "solution_digest": digest(sol),
+           "solution_absmax": float(np.max(np.abs(sol))).hex(), "sample_stride": FULL_SAMPLE_STRIDE}
+    st = FULL_SAMPLE_STRIDE
+    arrays[name + "/sample"] = np.ascontiguousarray(sol[::st, ::st, ::st])
+    b.close()
+    return rec
+
+
 def main():
+    only_full = "--full-only" in sys.argv
+    if only_full:  # add / refresh the 513^3 records without re-running everything else
+        with open(os.path.join(HERE, "golden.json")) as f:
+            gold = json.load(f)
+        arrays = dict(np.load(os.path.join(HERE, "fields.npz")))
+        gold["full"] = {}
+        for name, kw in FULL_CASES.items():
+            gold["full"][name] = full_case(name, kw, arrays)
+            print(name, gold["full"][name]["norms_repr"], flush=True)
+        with open(os.path.join(HERE, "golden.json"), "w") as f:
+            json.dump(gold, f, indent=1, sort_keys=True)
+        np.savez_compressed(os.path.join(HERE, "fields.npz"), **arrays)
+        print("wrote", len(arrays), "arrays")
+        return
     arrays = {}
     gold = {"generator": "tests/golden/make_golden.py", "source": "oracle/_ref/libgpusolve_ref.so (reference src/cpu/*.cpp)",
             "solve": {}, "operators": {}}
@@ -75,6 +105,10 @@ def main():
     for name, kw in OPERATOR_CASES.items():
         gold["operators"][name] = operator_case(name, kw, arrays)
         print(name, flush=True)
+    gold["full"] = {}
+    for name, kw in FULL_CASES.items():
+        gold["full"][name] = full_case(name, kw, arrays)
+        print(name, gold["full"][name]["norms_repr"], flush=True)
     with open(os.path.join(HERE, "golden.json"), "w") as f:
         json.dump(gold, f, indent=1, sort_keys=True)
     np.savez_compressed(os.path.join(HERE, "fields.npz"), **arrays)

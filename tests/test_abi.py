@@ -11,11 +11,12 @@ import pytest
 from cases import GOLDEN_DIR, ROOT
 
 HEADER = os.path.join(ROOT, "include", "gpusolve_cuda.h")
+HEADERS = sorted(os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include")) if f.endswith(".h"))
 CONF = os.path.join(GOLDEN_DIR, "data-2nd_order.conf")
 
 
 def declared_symbols():
-    src = open(HEADER).read()
+    src = "\n".join(open(h).read() for h in HEADERS)
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(gs_[A-Za-z_0-9]+)\s*\(", src)))
 
@@ -30,7 +31,7 @@ def test_header_declares_a_reasonable_surface():
 def test_library_exports_every_declared_symbol(gs):
     lib = C.CDLL(gs.LIB)
     for name in declared_symbols():
-        assert hasattr(lib, name), f"{name} declared in gpusolve_cuda.h but not exported"
+        assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
     assert set(gs.SIGNATURES) == set(declared_symbols()), "python binding and header drifted apart"
 
 

@@ -1,0 +1,30 @@
+#!/bin/bash
+# Round-2 first GPU visit (1 GPU): whole GPU suite incl. the prepared variants and the 513^3 parity cases, the new bench
+# line, A/B of the prepared variants, ncu evidence for modes 1/2.  Every step under its own timeout.
+# usage (under gpurun): bash tools/gpu_r02a.sh <tag>
+tag=${1:-r02a}
+out=gpurun_out
+mkdir -p $out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > $out/${tag}_smi.txt 2>&1
+nproc > $out/${tag}_nproc.txt; free -g >> $out/${tag}_nproc.txt; lscpu | head -20 >> $out/${tag}_nproc.txt
+GPUSOLVE_TEST_PREPARED=1 timeout 900 python -m pytest tests -m gpu -q -x --durations=15 > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $out/${tag}_pytest_gpu.log
+timeout 400 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench exit $?" >> $out/${tag}_bench.err
+timeout 200 python bench.py --impl reference > $out/${tag}_bench_ref.json 2> $out/${tag}_bench_ref.err
+for cfg in "" "GPUSOLVE_TAIL_POINTS=4096" "GPUSOLVE_TAIL_POINTS=40000" "GPUSOLVE_RR_VARIANT=2" "GPUSOLVE_TAIL_POINTS=4096 GPUSOLVE_RR_VARIANT=2"; do
+    name=$(echo "${cfg:-default}" | tr ' =' '__')
+    env $cfg timeout 100 python bench.py --steps 30 --warmup 5 --no-cpu --no-e2e --no-extras > $out/${tag}_ab_${name}.json 2> $out/${tag}_ab_${name}.err
+done
+for n in 63 127 255; do
+    for cfg in "" "GPUSOLVE_TAIL_POINTS=4096" "GPUSOLVE_TAIL_POINTS=40000"; do
+        name=$(echo "${cfg:-default}" | tr ' =' '__')
+        env $cfg timeout 60 python tools/profile_levels.py --n $n > $out/${tag}_levels_n${n}_${name}.txt 2>&1
+    done
+done
+timeout 100 python tools/profile_levels.py > $out/${tag}_levels.txt 2>&1
+timeout 100 python tools/profile_levels.py --mode 1 > $out/${tag}_levels_mode1.txt 2>&1
+timeout 100 python tools/profile_levels.py --mode 2 --pre 3 --post 3 > $out/${tag}_levels_mode2.txt 2>&1
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict|fas_rhs|restrict_simple' -c 10 \
+    -o $out/${tag}_mode1 -f python tools/one_cycle.py --n 511 --mode 1 > $out/${tag}_ncu_mode1.log 2>&1
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict' -c 6 --launch-skip 40 \
+    -o $out/${tag}_mode2 -f python tools/one_cycle.py --n 511 --mode 2 --pre 3 --post 3 > $out/${tag}_ncu_mode2.log 2>&1
+echo done
