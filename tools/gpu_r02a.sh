@@ -25,6 +25,6 @@ timeout 100 python tools/profile_levels.py --mode 1 > $out/${tag}_levels_mode1.t
 timeout 100 python tools/profile_levels.py --mode 2 --pre 3 --post 3 > $out/${tag}_levels_mode2.txt 2>&1
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict|fas_rhs|restrict_simple' -c 10 \
     -o $out/${tag}_mode1 -f python tools/one_cycle.py --n 511 --mode 1 > $out/${tag}_ncu_mode1.log 2>&1
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict' -c 6 --launch-skip 40 \
-    -o $out/${tag}_mode2 -f python tools/one_cycle.py --n 511 --mode 2 --pre 3 --post 3 > $out/${tag}_ncu_mode2.log 2>&1
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict|stencil_tma' -c 8 \
+    -o $out/${tag}_mode2 -f python tools/one_cycle.py --n 511 --mode 2 --pre 3 --post 3 --no-newton-step > $out/${tag}_ncu_mode2.log 2>&1
 echo done
