@@ -71,6 +71,13 @@ struct Level {
     int pre_valid;    // vtmp == this many Jacobi sweeps of v for the current f/aux (written by the fused sweep+norm kernels)
 };
 
+// a whole solve loop as one graph: initial norm, WHILE (conditional node) { V-cycle; stopping test }, history copy
+struct LoopGraph {
+    cudaGraphExec_t exec = nullptr;  // null: this configuration cannot loop on the device (cycle not parity neutral)
+    uint64_t launches_head = 0, launches_cycle = 0;
+    int pre_valid_after = 0;
+};
+
 struct EventPair {
     cudaEvent_t a, b;
     int op, level;
@@ -108,6 +115,10 @@ struct gs_handle {
     size_t stage_count;
     TailRec* tail;        // recorder of the coarse tail (cx.tune.tail_points > 0), made on first use
     int opt_overlap;      // slabs: ghost refresh on a second stream, overlapped with the interior of the operator that needs it
+    int opt_device_stop;  // solve loops without printing run as ONE conditional graph, stopping test on the device (kernels_ctl.cu)
+    StopCtl* d_stop;      // device-side loop state
+    StopCtl* h_stop;      // pinned copy, filled by the graph's last node
+    std::map<uint64_t, struct LoopGraph> loops;
     cudaStream_t stream2;
     cudaEvent_t ev_fork, ev_join;
 };
@@ -667,7 +678,7 @@ int tail_end(gs_handle* h)
 }
 
 // everything CpuSolver::vcycle (src/cpu/CpuSolver.cpp:85-139) does, queued on the stream
-int enqueue_vcycle_ops(gs_handle* h, int tail)
+int enqueue_vcycle_ops(gs_handle* h, int tail, bool host_norm)
 {
     const int last = (int)h->lev.size() - 1;
     for (int i = 0; i < last; i++) {
@@ -693,13 +704,13 @@ int enqueue_vcycle_ops(gs_handle* h, int tail)
         if (i - 1 == tail) GS(tail_end(h));
     }
     GS(do_norm_residual(h));
-    GS(norm_to_host(h, 0));
+    if (host_norm) GS(norm_to_host(h, 0));
     return GS_OK;
 }
 
-int enqueue_vcycle(gs_handle* h)
+int enqueue_vcycle(gs_handle* h, bool host_norm = true)
 {
-    const int rc = enqueue_vcycle_ops(h, tail_first_level(h));
+    const int rc = enqueue_vcycle_ops(h, tail_first_level(h), host_norm);
     if (h->cx.rec) {  // an operator failed while recording: drop the program, never leave the recorder attached
         h->cx.rec = nullptr;
     }
@@ -731,6 +742,9 @@ void drop_graphs(gs_handle* h)
     h->graphs_pre_valid.clear();
     h->graphs_gv.clear();
     h->graphs_swapped.clear();
+    for (auto& kv : h->loops)
+        if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    h->loops.clear();
 }
 
 int run_vcycle(gs_handle* h, double* norm)
@@ -804,8 +818,6 @@ int run_vcycle(gs_handle* h, double* norm)
     return GS_OK;
 }
 
-// the early-exit test exactly as spelled in src/cpu/CpuSolver.cpp:39 / src/cpu/NewtonSolver.cpp:37
-bool reached(double res, double initial, double tol) { return res <= initial / (1.0 / tol); }
 
 long long ms_since(std::chrono::high_resolution_clock::time_point t0)
 {
@@ -856,11 +868,169 @@ void print_partial_timers(gs_handle* h)
     memset(h->op_launches, 0, sizeof h->op_launches);
 }
 
+// the early-exit test exactly as spelled in src/cpu/CpuSolver.cpp:39 / src/cpu/NewtonSolver.cpp:37
+bool reached(double res, double initial, double tol) { return res <= initial / (1.0 / tol); }
+
+// ---- the solve loop on the device ---------------------------------------------------------------
+// One graph per (cycle state, maxiter, tol): [initial residual norm (fused with the first pre-smoothing pass) ;
+// stop_init] -> WHILE conditional node { captured V-cycle ; stop_check } -> copy of the loop state to pinned memory.
+// The body must leave the handle in the state it found it (buffer parity, fused pre-sweeps); it does for every
+// configuration the V-cycle graph itself is parity neutral for, otherwise the caller keeps the host loop.
+struct HostState {
+    std::vector<double*> v, t;
+    std::vector<int> gv;
+    int pre_valid;
+    uint64_t launches;
+};
+
+HostState save_state(const gs_handle* h)
+{
+    HostState st;
+    for (auto& L : h->lev) {
+        st.v.push_back(L.v);
+        st.t.push_back(L.vtmp);
+        st.gv.push_back(L.gv);
+    }
+    st.pre_valid = h->lev[0].pre_valid;
+    st.launches = h->launches;
+    return st;
+}
+
+void restore_state(gs_handle* h, const HostState& st)
+{
+    for (size_t l = 0; l < h->lev.size(); l++) {
+        h->lev[l].v = st.v[l];
+        h->lev[l].vtmp = st.t[l];
+        h->lev[l].gv = st.gv[l];
+        h->lev[l].vzero_next = false;
+    }
+    h->lev[0].pre_valid = st.pre_valid;
+    h->launches = st.launches;
+}
+
+bool same_buffers(const HostState& a, const HostState& b) { return a.v == b.v && a.t == b.t && a.pre_valid == b.pre_valid; }
+
+int build_loop_graph(gs_handle* h, uint64_t maxiter, double tol, LoopGraph* out)
+{
+    *out = LoopGraph();
+    if (!h->d_stop) {
+        CU(cudaMalloc((void**)&h->d_stop, sizeof(StopCtl)));
+        CU(cudaMallocHost((void**)&h->h_stop, sizeof(StopCtl)));
+    }
+    const HostState s0 = save_state(h);
+    cudaGraph_t g = nullptr;
+    CU(cudaGraphCreate(&g, 0));
+    cudaGraphConditionalHandle cond;
+    cudaError_t e = cudaGraphConditionalHandleCreate(&cond, g, 0, 0);
+    int rc = GS_OK;
+    cudaGraph_t body = nullptr, dummy = nullptr;
+    HostState sA = s0, sB = s0;
+    bool capturing = false;
+    do {
+        if (e != cudaSuccess) break;
+        // ---- head: initial norm + stop_init, the WHILE node, the history copy ----
+        if ((e = cudaStreamBeginCaptureToGraph(h->stream, g, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal)) != cudaSuccess) break;
+        capturing = true;
+        if ((rc = do_norm_residual(h)) != GS_OK) break;
+        if ((e = kc_stop_init(h->cx, h->d_stop, (unsigned long long)cond, (unsigned)maxiter)) != cudaSuccess) break;
+        cudaStreamCaptureStatus cs;
+        const cudaGraphNode_t* deps = nullptr;
+        size_t ndeps = 0;
+        if ((e = cudaStreamGetCaptureInfo_v2(h->stream, &cs, nullptr, nullptr, &deps, &ndeps)) != cudaSuccess) break;
+        cudaGraphNodeParams cp = {cudaGraphNodeTypeConditional};
+        cp.conditional.handle = cond;
+        cp.conditional.type = cudaGraphCondTypeWhile;
+        cp.conditional.size = 1;
+        cudaGraphNode_t cnode;
+        if ((e = cudaGraphAddNode(&cnode, g, deps, ndeps, &cp)) != cudaSuccess) break;
+        body = cp.conditional.phGraph_out[0];
+        if ((e = cudaStreamUpdateCaptureDependencies(h->stream, &cnode, 1, cudaStreamSetCaptureDependencies)) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(h->h_stop, h->d_stop, sizeof(StopCtl), cudaMemcpyDeviceToHost, h->stream)) != cudaSuccess) break;
+        e = cudaStreamEndCapture(h->stream, &dummy);
+        capturing = false;
+        if (e != cudaSuccess) break;
+        sA = save_state(h);
+        // ---- body: one V-cycle (no host copy of the norm) + stop_check ----
+        if ((e = cudaStreamBeginCaptureToGraph(h->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal)) != cudaSuccess) break;
+        capturing = true;
+        if ((rc = enqueue_vcycle(h, false)) != GS_OK) break;
+        if ((e = kc_stop_check(h->cx, h->d_stop, (unsigned long long)cond, (unsigned)maxiter, tol)) != cudaSuccess) break;
+        e = cudaStreamEndCapture(h->stream, &dummy);
+        capturing = false;
+        if (e != cudaSuccess) break;
+        sB = save_state(h);
+    } while (0);
+    if (capturing) {
+        cudaStreamEndCapture(h->stream, &dummy);
+        cudaGetLastError();
+    }
+    restore_state(h, s0);
+    if (rc == GS_OK && e == cudaSuccess && same_buffers(sA, sB)) {
+        cudaGraphExec_t ex = nullptr;
+        e = cudaGraphInstantiate(&ex, g, 0);
+        if (e == cudaSuccess) {
+            out->exec = ex;
+            out->launches_head = sA.launches - s0.launches;
+            out->launches_cycle = sB.launches - sA.launches;
+            out->pre_valid_after = sA.pre_valid;
+        }
+    }
+    cudaGraphDestroy(g);
+    if (rc != GS_OK) return rc;
+    if (e != cudaSuccess) {
+        // conditional nodes unavailable (old driver) or a body node they do not admit: not an error, the host loop runs
+        cudaGetLastError();
+        out->exec = nullptr;
+    }
+    return GS_OK;
+}
+
+// returns GS_OK with *used = false when this solve has to take the host loop
+int solve_mg_device(gs_handle* h, uint64_t maxiter, double tol, std::vector<double>* hist, uint64_t* cycles, bool* converged, bool* used)
+{
+    *used = false;
+    if (!h->opt_device_stop || !h->opt_graph || h->opt_timing || h->world != 1 || maxiter > (uint64_t)GS_STOP_CAP) return GS_OK;
+    if (smoother_km(h) == KM_NEWTON_COEF)
+        for (size_t l = 0; l < h->lev.size(); l++) GS(ensure_coef(h, (int)l));
+    uint64_t key = parity_key(h);
+    uint64_t tb;
+    memcpy(&tb, &tol, 8);
+    key = (key ^ maxiter) * 0x100000001b3ull;
+    key = (key ^ tb) * 0x100000001b3ull;
+    auto it = h->loops.find(key);
+    if (it == h->loops.end()) {
+        LoopGraph lg;
+        GS(build_loop_graph(h, maxiter, tol, &lg));
+        it = h->loops.emplace(key, lg).first;
+    }
+    const LoopGraph& lg = it->second;
+    if (!lg.exec) return GS_OK;
+    CU(cudaGraphLaunch(lg.exec, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    const StopCtl& c = *h->h_stop;
+    h->lev[0].pre_valid = lg.pre_valid_after;
+    h->launches += lg.launches_head + (uint64_t)c.count * lg.launches_cycle;
+    *cycles = c.count;
+    if (hist)
+        for (unsigned i = 0; i <= c.count; i++) hist->push_back(c.hist[i]);
+    *converged = c.count > 0 && reached(c.hist[c.count], c.initial, tol);
+    *h->h_norm = c.count > 0 ? c.hist[c.count] * c.hist[c.count] : c.initial * c.initial;
+    *used = true;
+    return GS_OK;
+}
+
 // CpuSolver::solve, src/cpu/CpuSolver.cpp:12-43
 int solve_mg(gs_handle* h, uint64_t maxiter, double tol, bool print, std::vector<double>* hist, uint64_t* cycles,
              bool* converged)
 {
     double initial;
+    if (!print) {
+        bool used = false;
+        *cycles = 0;
+        *converged = false;
+        GS(solve_mg_device(h, maxiter, tol, hist, cycles, converged, &used));
+        if (used) return GS_OK;
+    }
     GS(do_norm_residual(h));
     GS(norm_to_host(h, 0));
     CU(cudaStreamSynchronize(h->stream));
@@ -1025,6 +1195,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->stage_count = 0;
     h->tail = nullptr;
     h->cx.rec = nullptr;
+    h->opt_device_stop = 1;
+    if (const char* e = getenv("GPUSOLVE_DEVICE_STOP")) h->opt_device_stop = atoi(e) != 0;
+    h->d_stop = nullptr;
+    h->h_stop = nullptr;
     h->opt_overlap = 0;  // prepared, off until it has been through a multi-GPU run
     h->stream2 = nullptr;
     h->ev_fork = h->ev_join = nullptr;
@@ -1257,6 +1431,8 @@ int gs_destroy(gs_handle* h)
     if (h->cx.norm.ticket) cudaFree(h->cx.norm.ticket);
     if (h->cx.norm.result) cudaFree(h->cx.norm.result);
     if (h->h_norm) cudaFreeHost(h->h_norm);
+    if (h->d_stop) cudaFree(h->d_stop);
+    if (h->h_stop) cudaFreeHost(h->h_stop);
     for (auto& ep : h->ev_used) {
         cudaEventDestroy(ep.a);
         cudaEventDestroy(ep.b);
@@ -1654,6 +1830,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "overlap") h->opt_overlap = value != 0;
+    else if (n == "device_stop") h->opt_device_stop = value != 0;
     else if (n == "tail_points") h->cx.tune.tail_points = (int)std::max<int64_t>(0, std::min<int64_t>(1 << 20, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;

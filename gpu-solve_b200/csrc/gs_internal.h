@@ -84,6 +84,18 @@ struct LaunchCtx {
     TailRec* rec;         // non-null while the coarse tail is being recorded: ks_* append to it instead of launching
 };
 
+// ---- kernels_ctl.cu: device-side stopping test of the solve loop (conditional CUDA graph) ----
+constexpr int GS_STOP_CAP = 64;  // most cycles one device-side loop can run (its residual history is a fixed array)
+struct StopCtl {
+    double initial;               // norm before the first cycle
+    unsigned count, pad;          // cycles run
+    double hist[GS_STOP_CAP + 1]; // [0] initial, [i] after cycle i
+};
+// sqrt(cx.norm.result) -> initial / hist[0], loop condition = maxiter > 0
+cudaError_t kc_stop_init(const LaunchCtx& cx, StopCtl* c, unsigned long long cond, unsigned maxiter);
+// sqrt(cx.norm.result) -> hist[++count]; loop condition = !(res <= initial/(1/tol)) && count < maxiter
+cudaError_t kc_stop_check(const LaunchCtx& cx, StopCtl* c, unsigned long long cond, unsigned maxiter, double tol);
+
 // ---- kernels_simple.cu: one thread per lattice point, any 7 in-range offsets ----
 // All take LOCAL plane ranges [zb, ze) of points to update.
 cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,

@@ -307,6 +307,30 @@ def test_back_to_back_cycles_are_race_free(gs, mode, n):
         b.close()
 
 
+@pytest.mark.parametrize("name", ["lin_tol", "lin31_v22", "lin63_v33", "lin_ragged", "lin_pre0", "nl31_v22", "nl_even18", "nt_tol", "nt31_v22"])
+def test_device_side_stopping_equals_the_host_loop(name, gs, golden):
+    """device_stop = 1 (default): a solve that prints nothing — every inner solve of NewtonSolver::findError (<= 10 cycles,
+    tol 0.1, src/cpu/NewtonSolver.cpp:94-100), and CpuSolver::solve with print_progress = 0 — is ONE conditional CUDA graph
+    whose WHILE body is the V-cycle and whose stopping test `res <= r0/(1/tol)` runs on the device (kernels_ctl.cu).
+    Cycle counts, residual history and fields must equal the host loop's (and through it the reference's) exactly."""
+    kw, g = SOLVE_CASES[name], golden["solve"][name]
+    mode = kw["mode"]
+    res = []
+    for dstop in (1, 0):
+        dev = CudaBackend(gs, kernels=1, graph=1, **kw)
+        dev.set_option("device_stop", dstop)
+        l0 = dev.launches
+        info = dev.solve()
+        res.append((info.iterations, info.inner_cycles, info.converged, dev.history(), digest(dev.get(0, NEWTONV if mode == 2 else V)),
+                    dev.launches - l0))
+        dev.close()
+    assert res[0][:5] == res[1][:5], "device-side loop and host loop disagree"
+    assert res[0][5] > res[1][5], "the device loop adds its stop_init / stop_check launches to the same cycles"
+    assert res[0][0] == len(g["norms"]) - 1
+    if mode == 2:
+        assert res[0][1] == g["inner_cycles"]
+
+
 # Variants written while no GPU time was left (DESIGN.md section 9): default off, and so are their tests, which a
 # round-end run must not trip over.  GPUSOLVE_TEST_PREPARED=1 (tools/gpu_round.sh sets it) runs them.
 prepared = pytest.mark.skipif(os.environ.get("GPUSOLVE_TEST_PREPARED") != "1",

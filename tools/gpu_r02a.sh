@@ -7,7 +7,7 @@ out=gpurun_out
 mkdir -p $out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > $out/${tag}_smi.txt 2>&1
 nproc > $out/${tag}_nproc.txt; free -g >> $out/${tag}_nproc.txt; lscpu | head -20 >> $out/${tag}_nproc.txt
-GPUSOLVE_TEST_PREPARED=1 timeout 900 python -m pytest tests -m gpu -q -x --durations=15 > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $out/${tag}_pytest_gpu.log
+GPUSOLVE_TEST_PREPARED=1 timeout 900 python -m pytest tests -m gpu -q --durations=15 > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $out/${tag}_pytest_gpu.log
 timeout 400 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench exit $?" >> $out/${tag}_bench.err
 timeout 200 python bench.py --impl reference > $out/${tag}_bench_ref.json 2> $out/${tag}_bench_ref.err
 for cfg in "" "GPUSOLVE_TAIL_POINTS=4096" "GPUSOLVE_TAIL_POINTS=40000" "GPUSOLVE_RR_VARIANT=2" "GPUSOLVE_TAIL_POINTS=4096 GPUSOLVE_RR_VARIANT=2"; do
