@@ -54,6 +54,15 @@ static int fail(int code, const char* fmt, ...)
 // ---------------------------------------------------------------------------------
 // handle
 // ---------------------------------------------------------------------------------
+// slab boundaries: see gs_partition
+struct Partition {
+    int nlev;
+    int replicated_from;              // first level held whole by every rank
+    std::vector<std::vector<int>> b;  // b[level][rank] .. b[level][world]
+};
+
+constexpr int GS_LEVEL_ARRAYS = 8;  // v buffer A, v buffer B, f, r, restV, newtonV, coef, (spare)
+
 struct Level {
     Geom g;
     double h;
@@ -65,6 +74,7 @@ struct Level {
     bool replicated;  // whole level held (and computed) by every rank
     size_t count;     // doubles per array
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
+    double* phys[GS_LEVEL_ARRAYS];  // the arrays as allocated (v and vtmp trade places, these do not): index = slot registered with the peer transport
     bool coef_valid;
     int gv;           // slabs: ghost planes of v that are current on each side (0..2); refreshed lazily by need_v_halo
     bool vzero_next;  // enqueue_vcycle: v is to be zeroed before the pre-smoothing that follows (done inside its first pass if possible)
@@ -110,11 +120,16 @@ struct gs_handle {
     std::vector<uint64_t> lvl_launches;  // [level][op]
     std::vector<uint64_t> lvl_sweeps;    // [level] Jacobi sweeps run by the GS_OP_SMOOTH launches
     GsComm* comm;
+    Partition part;
     int replicated_from;
     double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
     size_t stage_count;
     TailRec* tail;        // recorder of the coarse tail (cx.tune.tail_points > 0), made on first use
     int opt_overlap;      // slabs: ghost refresh on a second stream, overlapped with the interior of the operator that needs it
+    int opt_p2p;          // slabs: ghost planes, coarse gather and norm through peer-mapped memory (kernels_comm.cu) instead of NCCL
+    std::vector<long long> arena_offs;  // byte offset of every registered array in the arena (index level * GS_LEVEL_ARRAYS + slot; last = newtonF)
+    char* arena;          // slabs: every level array lives in ONE allocation, shared with the peers by CUDA IPC
+    size_t arena_bytes;
     int opt_device_stop;  // solve loops without printing run as ONE conditional graph, stopping test on the device (kernels_ctl.cu)
     StopCtl* d_stop;      // device-side loop state
     StopCtl* h_stop;      // pinned copy, filled by the graph's last node
@@ -209,13 +224,6 @@ bool canonical_offsets(const gs_params& p)
     return true;
 }
 
-// slab boundaries: see gs_partition
-struct Partition {
-    int nlev;
-    int replicated_from;              // first level held whole by every rank
-    std::vector<std::vector<int>> b;  // b[level][rank] .. b[level][world]
-};
-
 Partition make_partition(const gs_params& p, int world)
 {
     Partition P;
@@ -302,14 +310,56 @@ bool partitioned(const gs_handle* h, int level) { return h->world > 1 && !h->lev
 
 // ---- multi-GPU helpers (no-ops on one GPU) ----------------------------------------
 // refresh `depth` ghost planes on both sides of a partitioned level array
+// registered index (peer transport) of a level array given by pointer, or -1
+int array_slot(const gs_handle* h, int level, const double* a)
+{
+    const Level& L = h->lev[level];
+    for (int k = 0; k < GS_LEVEL_ARRAYS; k++)
+        if (L.phys[k] == a) return level * GS_LEVEL_ARRAYS + k;
+    return -1;
+}
+
+// global plane of LOCAL plane 0 of rank r's slab on a partitioned level (create_impl: two ghost planes per side)
+int slab_z0(const gs_handle* h, int level, int r)
+{
+    if (r < 0 || r >= h->world) return 0;
+    return std::max(0, h->part.b[level][r] - 2);
+}
+
+bool use_p2p(const gs_handle* h) { return h->comm && h->opt_p2p && gs_comm_p2p(h->comm); }
+
+// queue the refresh of `depth` ghost planes on both sides of a partitioned level array on stream `s`; with the peer
+// transport the arrival is a separate step (exchange_arrive), which the overlapped path queues after the interior launch
+int exchange_send(gs_handle* h, int level, double* a, int depth, cudaStream_t s)
+{
+    Level& L = h->lev[level];
+    const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;  // local owned range
+    int rc;
+    const int k = use_p2p(h) ? array_slot(h, level, a) : -1;
+    if (k >= 0)
+        rc = gs_comm_halo_p2p(h->comm, k, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, L.g.z0, slab_z0(h, level, h->rank - 1),
+                              slab_z0(h, level, h->rank + 1), s);
+    else rc = gs_comm_halo(h->comm, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, s);
+    if (rc != 0) return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
+    h->launches += k >= 0 ? 1 : 0;
+    return GS_OK;
+}
+
+int exchange_arrive(gs_handle* h, int level, double* a, cudaStream_t s)
+{
+    if (!use_p2p(h) || array_slot(h, level, a) < 0) return GS_OK;  // NCCL send/recv completes in stream order
+    Level& L = h->lev[level];
+    if (gs_comm_halo_wait_p2p(h->comm, L.zlo, L.zhi, L.g.Zg, s) != 0)
+        return fail(GS_ECOMM, "halo wait failed on level %d: %s", level, gs_comm_error(h->comm));
+    h->launches += 1;
+    return GS_OK;
+}
+
 int exchange_halo(gs_handle* h, int level, double* a, int depth)
 {
     if (!partitioned(h, level)) return GS_OK;
-    Level& L = h->lev[level];
-    const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;  // local owned range
-    int rc = gs_comm_halo(h->comm, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, h->stream);
-    if (rc != 0) return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
-    return GS_OK;
+    GS(exchange_send(h, level, a, depth, h->stream));
+    return exchange_arrive(h, level, a, h->stream);
 }
 
 // make `depth` ghost planes of the level's v current (slabs only).  Operators that write v just mark the ghosts
@@ -339,9 +389,8 @@ int halo_begin(gs_handle* h, int level, int band, bool* started)
     if (L.ie - L.ib < (sides + 1) * band) return GS_OK;  // thin slab: plain exchange, one launch
     CU(cudaEventRecord(h->ev_fork, h->stream));
     CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
-    const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;
-    if (gs_comm_halo(h->comm, L.v, L.g.plane, lo, hi, 2, L.zlo, L.zhi, L.g.Zg, h->stream2) != 0)
-        return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
+    GS(exchange_send(h, level, L.v, 2, h->stream2));
+    GS(exchange_arrive(h, level, L.v, h->stream2));
     CU(cudaEventRecord(h->ev_join, h->stream2));
     *started = true;
     return GS_OK;
@@ -457,8 +506,11 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
 int norm_to_host(gs_handle* h, int level)
 {
     if (partitioned(h, level)) {
-        if (gs_comm_allreduce_sum(h->comm, h->cx.norm.result, 1, h->stream) != 0)
-            return fail(GS_ECOMM, "norm all-reduce failed: %s", gs_comm_error(h->comm));
+        // peer path: every rank adds the partial sums in rank order (bit-identical everywhere); else ncclAllReduce
+        const int rc = use_p2p(h) ? gs_comm_norm_p2p(h->comm, h->cx.norm.result, h->stream)
+                                  : gs_comm_allreduce_sum(h->comm, h->cx.norm.result, 1, h->stream);
+        if (rc != 0) return fail(GS_ECOMM, "norm reduction failed: %s", gs_comm_error(h->comm));
+        if (use_p2p(h)) h->launches += 2;
     }
     CU(cudaMemcpyAsync(h->h_norm, h->cx.norm.result, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     return GS_OK;
@@ -531,8 +583,11 @@ int finish_coarse(gs_handle* h, int level, double* coarse)
 {
     Level& C = h->lev[level + 1];
     if (partitioned(h, level) && C.replicated) {
-        if (gs_comm_gather_planes(h->comm, coarse, C.g.plane, level, h->stream) != 0)
-            return fail(GS_ECOMM, "coarse gather failed: %s", gs_comm_error(h->comm));
+        const int k = use_p2p(h) ? array_slot(h, level + 1, coarse) : -1;
+        const int rc = k >= 0 ? gs_comm_gather_planes_p2p(h->comm, k, coarse, C.g.plane, level, h->stream)
+                              : gs_comm_gather_planes(h->comm, coarse, C.g.plane, level, h->stream);
+        if (rc != 0) return fail(GS_ECOMM, "coarse gather failed: %s", gs_comm_error(h->comm));
+        if (k >= 0) h->launches += 2;
         return GS_OK;
     }
     return exchange_halo(h, level + 1, coarse, 1);
@@ -814,6 +869,7 @@ int run_vcycle(gs_handle* h, double* norm)
             if (swapped >> l & 1) std::swap(h->lev[l].v, h->lev[l].vtmp);
     }
     CU(cudaStreamSynchronize(h->stream));
+    if (h->comm && gs_comm_p2p_failed(h->comm)) return fail(GS_ECOMM, "a peer did not arrive at a ghost-plane exchange within the time limit");
     *norm = sqrt(*h->h_norm);
     return GS_OK;
 }
@@ -1195,6 +1251,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->stage_count = 0;
     h->tail = nullptr;
     h->cx.rec = nullptr;
+    h->arena = nullptr;
+    h->arena_bytes = 0;
+    h->opt_p2p = 1;
+    if (const char* e = getenv("GPUSOLVE_P2P")) h->opt_p2p = atoi(e) != 0;
     h->opt_device_stop = 1;
     if (const char* e = getenv("GPUSOLVE_DEVICE_STOP")) h->opt_device_stop = atoi(e) != 0;
     h->d_stop = nullptr;
@@ -1217,6 +1277,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* e = getenv("GPUSOLVE_GRAPH_MULTI")) h->opt_graph_multi = atoi(e) != 0;
 
     Partition part = make_partition(*p, world);
+    h->part = part;
     h->replicated_from = part.replicated_from;
     const int nlev = part.nlev;
     h->lev.resize(nlev);
@@ -1270,17 +1331,59 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
         k.preFac = p->stencil_val[0] / (L.h * L.h);  // :144
         k.omega = p->omega;
         k.gamma = p->gamma;
-        rc = alloc_zero(&L.v, L.count);
-        if (rc == GS_OK) rc = alloc_zero(&L.vtmp, L.count);
-        if (rc == GS_OK) rc = alloc_zero(&L.f, L.count);
-        if (rc == GS_OK) rc = alloc_zero(&L.r, L.count);
-        if (rc == GS_OK && p->mode == GS_MODE_NONLINEAR) rc = alloc_zero(&L.restV, L.count);
-        if (rc == GS_OK && p->mode == GS_MODE_NEWTON) rc = alloc_zero(&L.newtonV, L.count);
-        if (rc == GS_OK && p->mode == GS_MODE_NEWTON) rc = alloc_zero(&L.coef, L.count);
         size_t blocks = (size_t)((g.nx + 63) / 64) * ((g.ny + 3) / 4) * (size_t)g.nzl;
         max_blocks = std::max(max_blocks, blocks);
     }
-    if (rc == GS_OK && p->mode == GS_MODE_NEWTON) rc = alloc_zero(&h->newtonF, h->lev[0].count);
+    // ---- device memory.  One GPU: one allocation per array.  Slabs: ONE arena per rank (control block of the peer
+    // transport first, then every level array at a 2 MB-aligned offset), so that a single CUDA IPC handle maps all of a
+    // rank's arrays into its peers (gs_comm_enable_p2p).
+    {
+        const bool arena = world > 1;
+        std::vector<long long> offs((size_t)nlev * GS_LEVEL_ARRAYS + 1, -1);
+        size_t total = 1 << 16;  // P2PBlock
+        auto place = [&](size_t count) {
+            const size_t bytes = count * sizeof(double);
+            const size_t al = bytes >= ((size_t)2 << 20) ? ((size_t)2 << 20) : 4096;
+            total = (total + al - 1) / al * al;
+            const size_t at = total;
+            total += bytes;
+            return at;
+        };
+        for (int l = 0; l < nlev; l++) {
+            const bool want[GS_LEVEL_ARRAYS] = {true, true, true, true, p->mode == GS_MODE_NONLINEAR, p->mode == GS_MODE_NEWTON,
+                                                p->mode == GS_MODE_NEWTON, false};
+            for (int k = 0; k < GS_LEVEL_ARRAYS; k++)
+                if (want[k]) offs[(size_t)l * GS_LEVEL_ARRAYS + k] = (long long)place(h->lev[l].count);
+        }
+        if (p->mode == GS_MODE_NEWTON) offs[(size_t)nlev * GS_LEVEL_ARRAYS] = (long long)place(h->lev[0].count);
+        if (arena) {
+            cudaError_t ae = cudaMalloc((void**)&h->arena, total);
+            if (ae != cudaSuccess) rc = fail(GS_ENOMEM, "cudaMalloc of the %zu-byte slab arena failed: %s", total, cudaGetErrorString(ae));
+            else if ((ae = cudaMemset(h->arena, 0, total)) != cudaSuccess) rc = fail(GS_ECUDA, "arena memset: %s", cudaGetErrorString(ae));
+            h->arena_bytes = total;
+        }
+        for (int l = 0; l < nlev && rc == GS_OK; l++) {
+            Level& L = h->lev[l];
+            for (int k = 0; k < GS_LEVEL_ARRAYS && rc == GS_OK; k++) {
+                const long long o = offs[(size_t)l * GS_LEVEL_ARRAYS + k];
+                if (o < 0) continue;
+                if (arena) L.phys[k] = (double*)(h->arena + o);
+                else rc = alloc_zero(&L.phys[k], L.count);
+            }
+            L.v = L.phys[0];
+            L.vtmp = L.phys[1];
+            L.f = L.phys[2];
+            L.r = L.phys[3];
+            L.restV = L.phys[4];
+            L.newtonV = L.phys[5];
+            L.coef = L.phys[6];
+        }
+        if (rc == GS_OK && p->mode == GS_MODE_NEWTON) {
+            if (arena) h->newtonF = (double*)(h->arena + offs[(size_t)nlev * GS_LEVEL_ARRAYS]);
+            else rc = alloc_zero(&h->newtonF, h->lev[0].count);
+        }
+        h->arena_offs = offs;
+    }
     if (rc != GS_OK) {
         gs_destroy(h);
         return rc;
@@ -1340,6 +1443,13 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
             int code = fail(GS_ECOMM, "communicator setup failed: %s", h->comm ? gs_comm_error(h->comm) : "out of memory");
             gs_destroy(h);
             return code;
+        }
+        // peer-mapped transport: every rank maps every other rank's arena (CUDA IPC).  All ranks decide together; if any
+        // of them cannot (no peer access between the devices), all keep NCCL send/recv and say so once.
+        if (h->opt_p2p && cudaDeviceSynchronize() == cudaSuccess &&
+            gs_comm_enable_p2p(h->comm, h->arena, h->arena_bytes, h->arena_offs.data(), (int)h->arena_offs.size(), h->cx.sm_count,
+                               h->stream) != 0) {
+            if (rank == 0) fprintf(stderr, "gpusolve: %s; ghost planes travel by NCCL send/recv\n", gs_comm_error(h->comm));
         }
     }
     // the zero fills above ran on the legacy stream, which the handle's non-blocking stream does not wait for
@@ -1419,13 +1529,15 @@ int gs_destroy(gs_handle* h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     drop_graphs(h);
+    if (h->comm && h->stream) gs_comm_disable_p2p(h->comm, h->stream);  // collective: peers unmap this arena before it is freed
     for (auto& L : h->lev)
-        for (double* a : {L.v, L.vtmp, L.f, L.r, L.restV, L.newtonV, L.coef})
+        for (double* a : L.phys)
             if (a) {
                 gs_tensor_map_drop(a);  // the address may come back from a later cudaMalloc with another geometry
-                cudaFree(a);
+                if (!h->arena) cudaFree(a);
             }
-    if (h->newtonF) cudaFree(h->newtonF);
+    if (h->newtonF && !h->arena) cudaFree(h->newtonF);
+    if (h->arena) cudaFree(h->arena);
     if (h->stage) cudaFree(h->stage);
     if (h->cx.norm.partials) cudaFree(h->cx.norm.partials);
     if (h->cx.norm.ticket) cudaFree(h->cx.norm.ticket);
@@ -1831,6 +1943,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "overlap") h->opt_overlap = value != 0;
     else if (n == "device_stop") h->opt_device_stop = value != 0;
+    else if (n == "p2p") h->opt_p2p = value != 0;
     else if (n == "tail_points") h->cx.tune.tail_points = (int)std::max<int64_t>(0, std::min<int64_t>(1 << 20, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;
