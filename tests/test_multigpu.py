@@ -32,6 +32,12 @@ def _torchrun(world, args, env):
 def test_slab_solver_equals_one_gpu(gs, world, mode, transport):
     if _ngpu(gs) < world:
         pytest.skip(f"needs {world} GPUs")
+    only = os.environ.get("GPUSOLVE_TEST_WORLDS")  # e.g. "3,4": restrict an expensive multi-GPU visit
+    if only and str(world) not in only.split(","):
+        pytest.skip("world not selected by GPUSOLVE_TEST_WORLDS")
+    only_t = os.environ.get("GPUSOLVE_TEST_TRANSPORTS")
+    if only_t and transport not in only_t.split(","):
+        pytest.skip("transport not selected by GPUSOLVE_TEST_TRANSPORTS")
     env = {"GPUSOLVE_SLAB_MIN_POINTS": "0", "GPUSOLVE_P2P": "1" if "p2p" in transport else "0",
            "GPUSOLVE_OVERLAP": "1" if "overlap" in transport else "0"}
     pre = "3" if mode == 2 else "2"
