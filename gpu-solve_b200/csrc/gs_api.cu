@@ -308,6 +308,10 @@ int smoother_km(const gs_handle* h)
 
 bool partitioned(const gs_handle* h, int level) { return h->world > 1 && !h->lev[level].replicated; }
 
+// offsets argument of the single-sweep tuned kernels (kernels_fast.cu): null = canonical axis-aligned stencil, else the
+// config's seven offsets (GEN instantiations)
+const StencilOff* gen_offsets(const gs_handle* h) { return h->canonical ? nullptr : &h->so; }
+
 // ---- multi-GPU helpers (no-ops on one GPU) ----------------------------------------
 // refresh `depth` ghost planes on both sides of a partitioned level array
 // registered index (peer transport) of a level array given by pointer, or -1
@@ -438,7 +442,8 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     }
     L.pre_valid = 0;
     const double* aux = smoother_aux(h, level, km);
-    const bool tuned = h->opt_kernels && h->canonical && !h->cx.rec;  // the tail records the one-thread-per-point operators
+    const bool tuned1 = h->opt_kernels && !h->cx.rec;  // the tail records the one-thread-per-point operators
+    const bool tuned = tuned1 && h->canonical;         // two sweeps per pass: canonical stencil only
     if (L.vzero_next) {
         // CpuSolver.cpp:100-101 v.fill(0) followed by the pre-smoothing: the two-sweep kernel takes the zero iterate as a
         // constant (no memset, no read of v); its output buffer becomes v, the stale one is only ever written again
@@ -491,7 +496,7 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
             }
         }
         if (!handled) {
-            if (tuned) CU(kf_smooth(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
+            if (tuned1) CU(kf_smooth(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled, gen_offsets(h)));
             if (!handled) CU(ks_smooth(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.vtmp, L.f, aux));
             iters--;
             h->lvl_sweeps[level]++;
@@ -525,8 +530,9 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     OpScope t(h, GS_OP_RESIDUAL, level);
     GS(need_v_halo(h, level, 1));
     bool handled = false;
-    if (h->opt_kernels && h->canonical && !h->cx.rec)
-        CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled));
+    if (h->opt_kernels && !h->cx.rec)
+        CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled,
+                       gen_offsets(h)));
     if (!handled)
         CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr));
     return GS_OK;
@@ -539,20 +545,20 @@ int do_norm_residual(gs_handle* h)
 {
     Level& L = h->lev[0];
     const int km = smoother_km(h);
-    if (h->opt_fuse_norm && h->opt_kernels && h->canonical && h->p.pre > 0 && !L.pre_valid) {
+    if (h->opt_fuse_norm && h->opt_kernels && h->p.pre > 0 && !L.pre_valid) {
         if (km == KM_NEWTON_COEF) GS(ensure_coef(h, 0));
         OpScope t(h, GS_OP_RESIDUAL, 0);
         bool handled = false;
         const double* aux = smoother_aux(h, 0, km);
-        GS(need_v_halo(h, 0, (h->p.pre >= 2 && h->cx.tune.fuse2) ? 2 : 1));
-        if (h->p.pre >= 2 && (!partitioned(h, 0) || L.gv >= 2)) {
+        GS(need_v_halo(h, 0, (h->p.pre >= 2 && h->cx.tune.fuse2 && h->canonical) ? 2 : 1));
+        if (h->p.pre >= 2 && h->canonical && (!partitioned(h, 0) || L.gv >= 2)) {
             CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, false, &handled));
             if (handled) {
                 L.pre_valid = 2;
                 return GS_OK;
             }
         }
-        CU(kf_smooth_norm(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled));
+        CU(kf_smooth_norm(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled, gen_offsets(h)));
         if (handled) {
             L.pre_valid = 1;
             return GS_OK;
@@ -648,7 +654,13 @@ int do_restrict_residual(gs_handle* h, int level)
         CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
         if (handled) return finish_coarse(h, level, C.f);
     }
-    CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
+    {
+        // unfused: the residual goes to memory (config-driven offsets: GEN kernel; small levels: one thread per point)
+        bool handled = false;
+        if (h->opt_kernels && !h->canonical && !h->cx.rec)
+            CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), L.r, &handled, gen_offsets(h)));
+        if (!handled) CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
+    }
     GS(do_restrict(h, level, L.r, C.f, nullptr));
     return GS_OK;
 }

@@ -140,13 +140,16 @@ bool kf_available();
 // one-time per-process setup (dynamic shared memory attributes); call outside stream capture
 cudaError_t kf_prepare();
 cudaError_t kf_smooth(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
-                      const double* vin, double* vout, const double* f, const double* aux, bool* handled);
+                      const double* vin, double* vout, const double* f, const double* aux, bool* handled, const StencilOff* gen = nullptr);
 // r = f - A(v) (stored if r != nullptr) and sum of squares -> cx.norm.result
 cudaError_t kf_residual(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
-                        const double* v, const double* f, const double* aux, double* r, bool* handled);
+                        const double* v, const double* f, const double* aux, double* r, bool* handled, const StencilOff* gen = nullptr);
 // vout = sweep(vin) and sum of squares of the residual of vin -> cx.norm.result
 cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
-                           const double* vin, double* vout, const double* f, const double* aux, bool* handled);
+                           const double* vin, double* vout, const double* f, const double* aux, bool* handled,
+                           const StencilOff* gen = nullptr);
+// `gen` != nullptr in the three calls above: the config's seven offsets (any taps inside the one-cell rim) instead of the
+// canonical axis-aligned stencil — the GEN instantiations of stencil_tma
 
 // ---- kernels_fused.cu: two Jacobi sweeps per pass (temporal blocking, bit-identical to two single sweeps) ----
 cudaError_t kx_prepare();

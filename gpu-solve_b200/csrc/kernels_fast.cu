@@ -140,6 +140,8 @@ struct FastP {
     const double* f;
     const double* aux;
     NormBuf nb;    // OP_RESID
+    bool gen;                    // config-driven offsets: take the GEN kernels
+    int gdx[7], gdy[7], gdz[7];  // GEN kernels: the config's seven offsets (src/gridParams.h:7-26), each in {-1,0,1}
 };
 
 template <int KM, int AR>
@@ -197,7 +199,12 @@ struct TmaCfg {
     static constexpr int THREADS = CONSUMERS + 32;
 };
 
-template <int KM, int AR, int OP, int TX, int TY, int NSTAGE>
+// GEN: config-driven offsets (any seven taps inside the one-cell rim, src/gridParams.h:7-26, src/main.cpp:63-82).  The v
+// box already carries the full xy rim and the ring holds planes z-1, z, z+1, so tap i is one shared-memory read at the
+// CTA-uniform displacement (dx_i, dy_i) in the box of plane z+dz_i; the sum runs over i = 0..6 in config order like the
+// reference (src/cpu/CpuSolver.cpp:56-60), hence the same bits as kernels_simple.cu.  The only structural difference
+// from the canonical kernel: a stage is released one step later (plane q-1 is still read at step q).
+template <int KM, int AR, int OP, int TX, int TY, int NSTAGE, bool GEN = false>
 __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant__ CUtensorMap map_v,
                                                             const __grid_constant__ CUtensorMap map_f, FastP p)
 {
@@ -255,14 +262,45 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
     double D = vbox(0)[ctr];  // (stage 0 is released at the end of the first iteration, once D has been used)
     mbar_wait(&full[1 % NSTAGE], (1 / NSTAGE) & 1);
     double C = vbox(1)[ctr];
+    int goff[7];  // GEN: displacement of tap i inside a v box
+    if (GEN) {
+#pragma unroll
+        for (int i = 0; i < 7; i++) goff[i] = ctr + p.gdy[i] * Cfg::VW + p.gdx[i];
+    }
 
     for (int q = 1; q <= nz; q++) {
         const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
         mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
         const double* vb = vbox(q);
         const double U = vbox(q + 1)[ctr];
-        const double E = vb[ctr + 1], W = vb[ctr - 1], N = vb[ctr + Cfg::VW], S = vb[ctr - Cfg::VW];
         const double fv = fbox(q)[ty * TX + tx];
+        if (GEN) {
+            const double* vd = vbox(q - 1);
+            const double* vu = vbox(q + 1);
+            double s = 0.0;
+#pragma unroll
+            for (int i = 0; i < 7; i++) {
+                const double* b = p.gdz[i] < 0 ? vd : (p.gdz[i] > 0 ? vu : vb);
+                s += p.k.c[i] * b[goff[i]];
+            }
+            double den;
+            const double r = finish_residual<KM, AR>(s, C, fv, aux, p.k, den);
+            if (live) {
+                if (OP == OP_RESID) {
+                    if (p.vout) p.vout[c] = r;
+                } else {
+                    p.vout[c] = jacobi_update<KM>(C, r, den, p.k);
+                }
+                if (OP != OP_SMOOTH) sq += r * r;
+            }
+            __syncwarp();
+            if (lane0) mbar_arrive(&empty[(q - 1) % NSTAGE]);  // plane q-1 was read in this step for the last time
+            D = C;
+            C = U;
+            c += p.g.plane;
+            continue;
+        }
+        const double E = vb[ctr + 1], W = vb[ctr - 1], N = vb[ctr + Cfg::VW], S = vb[ctr - Cfg::VW];
         if (OP == OP_SMOOTH) {
             const double nv = point_update<KM, AR>(C, E, W, N, S, U, D, fv, aux, p.k);
             if (live) p.vout[c] = nv;
@@ -304,7 +342,7 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
 // ---------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------
-template <int KM, int AR, int OP, int TX, int TY, int NSTAGE>
+template <int KM, int AR, int OP, int TX, int TY, int NSTAGE, bool GEN = false>
 cudaError_t launch_tma(const LaunchCtx& cx, FastP p, bool* handled)
 {
     using Cfg = TmaCfg<TX, TY, NSTAGE>;
@@ -313,10 +351,10 @@ cudaError_t launch_tma(const LaunchCtx& cx, FastP p, bool* handled)
     static DevOnce once;
     int occ = 1;
     cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
-        cudaError_t e = cudaFuncSetAttribute(stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(stencil_tma<KM, AR, OP, TX, TY, NSTAGE, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, stencil_tma<KM, AR, OP, TX, TY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, stencil_tma<KM, AR, OP, TX, TY, NSTAGE, GEN>, Cfg::THREADS, Cfg::SMEM);
         return e;
     });
     if (pe != cudaSuccess) return pe;
@@ -329,7 +367,7 @@ cudaError_t launch_tma(const LaunchCtx& cx, FastP p, bool* handled)
     const int nzc = (p.ze - p.zb + p.zchunk - 1) / p.zchunk;
     dim3 grid((p.g.nx + TX - 1) / TX, (p.g.ny + TY - 1) / TY, nzc);
     if (OP != OP_SMOOTH && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;  // not handled
-    stencil_tma<KM, AR, OP, TX, TY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    stencil_tma<KM, AR, OP, TX, TY, NSTAGE, GEN><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
     *handled = true;
     return cudaGetLastError();
 }
@@ -351,9 +389,18 @@ cudaError_t launch_zmarch(const LaunchCtx& cx, FastP p, bool* handled)
 // id, BX, BY
 #define ZMARCH_VARIANTS(X) X(1, 64, 4) X(13, 64, 8)
 
+template <int KM, int AR, int OP>
+cudaError_t dispatch_gen(const LaunchCtx& cx, const FastP& p, bool* handled)
+{
+    // one more stage than the canonical kernels: three planes are being read, two are in flight
+    if (p.g.nx >= 96) return launch_tma<KM, AR, OP, 128, 4, 5, true>(cx, p, handled);
+    return launch_tma<KM, AR, OP, 64, 4, 5, true>(cx, p, handled);
+}
+
 template <int KM, int AR>
 cudaError_t dispatch_smooth(const LaunchCtx& cx, const FastP& p, int variant, bool* handled)
 {
+    if (p.gen) return dispatch_gen<KM, AR, OP_SMOOTH>(cx, p, handled);
     switch (variant) {
 #define X(id, bx, by) \
     case id: return launch_zmarch<KM, AR, bx, by>(cx, p, handled);
@@ -370,6 +417,7 @@ cudaError_t dispatch_smooth(const LaunchCtx& cx, const FastP& p, int variant, bo
 template <int KM, int AR, int OP>
 cudaError_t dispatch_resid(const LaunchCtx& cx, const FastP& p, bool* handled)
 {
+    if (p.gen) return dispatch_gen<KM, AR, OP>(cx, p, handled);
     // wide tiles on big levels, the narrow tile where 128 columns would leave most of a CTA idle
     if (p.g.nx >= 96) return launch_tma<KM, AR, OP, 128, 4, 4>(cx, p, handled);
     return launch_tma<KM, AR, OP, 64, 4, 4>(cx, p, handled);
@@ -388,8 +436,18 @@ cudaError_t dispatch_resid(const LaunchCtx& cx, const FastP& p, bool* handled)
 
 }  // namespace
 
+static void set_gen(FastP& p, const StencilOff* so)
+{
+    p.gen = so != nullptr;
+    for (int i = 0; i < 7; i++) {
+        p.gdx[i] = so ? so->dx[i] : 0;
+        p.gdy[i] = so ? so->dy[i] : 0;
+        p.gdz[i] = so ? so->dz[i] : 0;
+    }
+}
+
 cudaError_t kf_smooth(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
-                      double* vout, const double* f, const double* aux, bool* handled)
+                      double* vout, const double* f, const double* aux, bool* handled, const StencilOff* gen)
 {
     *handled = false;
     if (vin) {
@@ -398,6 +456,7 @@ cudaError_t kf_smooth(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb
         if (g.nx < cx.tune.fast_min_n || g.ny < 8 || ze - zb < 8) return cudaSuccess;
     }
     FastP p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm};
+    set_gen(p, gen);
     p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
     if (vin && p.zchunk > ze - zb) p.zchunk = ze - zb;
     int variant = cx.tune.smooth_variant;
@@ -411,7 +470,7 @@ cudaError_t kf_smooth(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb
 }
 
 cudaError_t kf_residual(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* v,
-                        const double* f, const double* aux, double* r, bool* handled)
+                        const double* f, const double* aux, double* r, bool* handled, const StencilOff* gen)
 {
     *handled = false;
     if (v) {
@@ -419,6 +478,7 @@ cudaError_t kf_residual(const LaunchCtx& cx, int km, int ar, const Geom& g, int 
         if (g.nx < cx.tune.fast_min_n || g.ny < 8 || ze - zb < 8) return cudaSuccess;
     }
     FastP p{g, k, zb, ze, 0, v, r, f, aux, cx.norm};
+    set_gen(p, gen);
     p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
     if (v && p.zchunk > ze - zb) p.zchunk = ze - zb;
     cudaError_t e = cudaSuccess;
@@ -432,7 +492,7 @@ cudaError_t kf_residual(const LaunchCtx& cx, int km, int ar, const Geom& g, int 
 // vout = one Jacobi sweep of vin, and sum of squares of the residual of vin -> cx.norm.result: the residual the
 // V-cycle returns (src/cpu/CpuSolver.cpp:138) is the one the next cycle's first pre-smoothing sweep starts from (:88)
 cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
-                           const double* vin, double* vout, const double* f, const double* aux, bool* handled)
+                           const double* vin, double* vout, const double* f, const double* aux, bool* handled, const StencilOff* gen)
 {
     *handled = false;
     if (vin) {
@@ -440,6 +500,7 @@ cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, i
         if (g.nx < cx.tune.fast_min_n || g.ny < 8 || ze - zb < 8) return cudaSuccess;
     }
     FastP p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm};
+    set_gen(p, gen);
     p.zchunk = cx.tune.zchunk > 0 ? cx.tune.zchunk : 64;
     if (vin && p.zchunk > ze - zb) p.zchunk = ze - zb;
     cudaError_t e = cudaSuccess;
@@ -464,12 +525,16 @@ cudaError_t kf_prepare()
         for (int pw = 0; pw < 8 && e == cudaSuccess; pw++) {
             for (int var : variants) {
                 cx.tune.smooth_variant = var;
-                if (e == cudaSuccess) e = kf_smooth(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+                if (e == cudaSuccess) e = kf_smooth(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled, nullptr);
             }
+            StencilOff so{};
             for (int nx : {64, 128}) {
                 g.nx = nx;
-                if (e == cudaSuccess) e = kf_residual(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
-                if (e == cudaSuccess) e = kf_smooth_norm(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled);
+                for (const StencilOff* gen : {(const StencilOff*)nullptr, (const StencilOff*)&so}) {
+                    if (e == cudaSuccess) e = kf_residual(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled, gen);
+                    if (e == cudaSuccess) e = kf_smooth_norm(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled, gen);
+                    if (e == cudaSuccess && gen) e = kf_smooth(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, &handled, gen);
+                }
             }
             g.nx = 0;
         }

@@ -16,6 +16,8 @@ CANON_OFFSETS = ((0, 0, 0), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0,
 # a permuted, non-symmetric 7-point stencil: exercises config-driven offsets and summation order
 SKEW_VALUES = (6.5, -1.1, -0.9, -1.2, -0.8, -1.3, -0.7)
 SKEW_OFFSETS = ((0, 0, 0), (0, 0, 1), (1, 0, 0), (0, -1, 0), (-1, 0, 0), (0, 1, 0), (0, 0, -1))
+# the same with a zero row sum (a consistent second-order operator plus first-order terms): multigrid still converges
+NC_VALUES = (6.0, -1.1, -0.9, -1.2, -0.8, -1.3, -0.7)
 # offsets off the axes (still inside the one-cell halo)
 DIAG_OFFSETS = ((0, 0, 0), (1, 1, 0), (-1, -1, 0), (0, 1, 1), (0, -1, -1), (1, 0, 1), (-1, 0, -1))
 
@@ -52,6 +54,11 @@ BIG_CASES = {
     "lin_wide_v44": dict(n=(131, 97, 63), mode=0, pre=4, post=4, maxiter=2, tol=1e-30),
     "nl_wide_v42": dict(n=(121, 64, 70), mode=1, pre=4, post=2, maxiter=2, tol=1e-30),
     "nt_wide_v24": dict(n=(100, 90, 47), mode=2, pre=2, post=4, maxiter=2, tol=1e-30),
+    # config-driven (non-canonical) offsets on grids large enough for the tuned GEN kernels (kernels_fast.cu stencil_tma<.., GEN>)
+    "lin_skew127_v22": dict(n=127, mode=0, pre=2, post=2, maxiter=2, tol=1e-30, values=NC_VALUES, offsets=SKEW_OFFSETS),
+    "lin_diag_wide_v31": dict(n=(131, 97, 63), mode=0, pre=3, post=1, maxiter=2, tol=1e-30, values=NC_VALUES, offsets=DIAG_OFFSETS),
+    "nl_diag100_v22": dict(n=(100, 90, 47), mode=1, pre=2, post=2, maxiter=1, tol=1e-30, values=NC_VALUES, offsets=DIAG_OFFSETS),
+    "nt_skew100_v22": dict(n=(100, 90, 47), mode=2, pre=2, post=2, maxiter=1, tol=1e-30, values=NC_VALUES, offsets=SKEW_OFFSETS),
 }
 
 # BASELINE.json configs[1]-[3] at their full size (arrays 513^3): one script per mode (backends.full_size_script), run
@@ -85,6 +92,11 @@ OPERATOR_CASES = {
     "op_lin_wide_even": dict(n=(120, 56, 34), mode=0),
     "op_nl_wide": dict(n=(125, 40, 33), mode=1),
     "op_nt_wide": dict(n=(100, 35, 20), mode=2),
+    # config-driven offsets through the tuned GEN kernels
+    "op_lin_skew_mid": dict(n=(70, 53, 41), mode=0, values=NC_VALUES, offsets=SKEW_OFFSETS),
+    "op_lin_diag_wide": dict(n=(130, 61, 40), mode=0, values=NC_VALUES, offsets=DIAG_OFFSETS),
+    "op_nl_diag_mid": dict(n=(67, 50, 38), mode=1, values=NC_VALUES, offsets=DIAG_OFFSETS),
+    "op_nt_skew_mid": dict(n=(63, 49, 35), mode=2, values=NC_VALUES, offsets=SKEW_OFFSETS),
 }
 
 

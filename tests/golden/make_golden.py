@@ -82,6 +82,22 @@ def full_case(name, kw, arrays):
 
 
 def main():
+    if "--missing" in sys.argv:  # add the records of cases that golden.json does not hold yet
+        with open(os.path.join(HERE, "golden.json")) as f:
+            gold = json.load(f)
+        arrays = dict(np.load(os.path.join(HERE, "fields.npz")))
+        for name, kw in {**SOLVE_CASES, **BIG_CASES}.items():
+            if name not in gold["solve"]:
+                gold["solve"][name] = solve_case(name, kw, arrays)
+                print(name, gold["solve"][name]["norms_repr"][:3], flush=True)
+        for name, kw in OPERATOR_CASES.items():
+            if name not in gold["operators"]:
+                gold["operators"][name] = operator_case(name, kw, arrays)
+                print(name, flush=True)
+        with open(os.path.join(HERE, "golden.json"), "w") as f:
+            json.dump(gold, f, indent=1, sort_keys=True)
+        np.savez_compressed(os.path.join(HERE, "fields.npz"), **arrays)
+        return
     only_full = "--full-only" in sys.argv
     if only_full:  # add / refresh the 513^3 records without re-running everything else
         with open(os.path.join(HERE, "golden.json")) as f:
