@@ -605,7 +605,9 @@ int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, dou
     Level& C = h->lev[level + 1];
     int zb, ze;
     coarse_range(h, level, &zb, &ze);
-    CU(ks_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2));
+    bool handled = false;
+    if (h->opt_kernels && !h->cx.rec) CU(kt_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2, &handled));
+    if (!handled) CU(ks_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2));
     GS(finish_coarse(h, level, coarse));
     if (coarse2) GS(finish_coarse(h, level, coarse2));
     return GS_OK;

@@ -163,5 +163,7 @@ cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int z
 cudaError_t kt_prepare();
 cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* vin,
                                double* vout, const double* coarse, bool* handled);
+cudaError_t kt_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zcb, int zce, const double* fine, double* coarse,
+                        double* coarse2, bool* handled);
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
                               const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled);

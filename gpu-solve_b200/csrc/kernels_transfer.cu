@@ -123,6 +123,76 @@ cudaError_t prolong_occ(int* occ)
 }
 
 // ---------------------------------------------------------------------------------
+// plain full-weighting restriction (of v in the FAS coarse right-hand side, of newtonV down the hierarchy, of a stored
+// residual when the stencil offsets are config-driven)
+// ---------------------------------------------------------------------------------
+// src/cpu/CpuSolver.cpp:211-238.  One thread per coarse column (X,Y), marching along coarse z: the nine fine values of
+// fine plane 2Z+1 are the plane 2(Z+1)-1 of the next coarse point, so every fine plane is loaded once per thread —
+// rows as an aligned double2 (x = 2X-1, 2X) plus the scalar x = 2X+1, which the neighbouring thread also loads (L1 hit).
+// The 27-term sum runs in the reference's order (x offset outermost, z innermost, weights 0.125*w*w*w evaluated left to
+// right), so the result is bit-identical to kernels_simple.cu restrict_point.  Up to two outputs (FAS: restV and v).
+struct RestrictFastP {
+    Geom gf, gc;
+    int zcb, zce, zchunk;  // LOCAL coarse planes [zcb, zce), planes per CTA
+    const double* fine;
+    double* coarse;
+    double* coarse2;
+};
+
+constexpr int RBX = 32, RBY = 8;
+DevOnce g_restrict_once;
+
+struct Nine {
+    double v[3][3];  // [x offset -1,0,+1][y offset -1,0,+1]
+};
+
+__device__ __forceinline__ Nine load_nine(const double* __restrict__ f, i64 c, i64 pitch)
+{
+    // c = element (2X-1, 2Y-1) of the plane: 16-byte aligned (x = 2X-1 is odd, GS_XOFF + x even)
+    Nine n;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        const double2 a = __ldg(reinterpret_cast<const double2*>(f + c + j * pitch));
+        n.v[0][j] = a.x;
+        n.v[1][j] = a.y;
+        n.v[2][j] = __ldg(f + c + j * pitch + 2);
+    }
+    return n;
+}
+
+__global__ void __launch_bounds__(RBX* RBY) restrict_zmarch(RestrictFastP p)
+{
+    const int X = blockIdx.x * RBX + threadIdx.x + 1, Y = blockIdx.y * RBY + threadIdx.y + 1;
+    if (X > p.gc.nx || Y > p.gc.ny) return;
+    const int zc0 = p.zcb + blockIdx.z * p.zchunk;
+    const int zc1 = min(zc0 + p.zchunk, p.zce);
+    const int zf = 2 * (zc0 + p.gc.z0) - p.gf.z0;  // local fine plane of the first centre
+    i64 c = gs_idx(p.gf, 2 * X - 1, 2 * Y - 1, zf - 1);
+    i64 cc = gs_idx(p.gc, X, Y, zc0);
+    const i64 pitch = p.gf.pitch, plane = p.gf.plane;
+    Nine A = load_nine(p.fine, c, pitch);
+    for (int zc = zc0; zc < zc1; zc++) {
+        const Nine B = load_nine(p.fine, c + plane, pitch);
+        const Nine C = load_nine(p.fine, c + 2 * plane, pitch);
+        double acc = 0.0;
+        const double w[3] = {0.5, 1.0, 0.5};
+#pragma unroll
+        for (int ii = 0; ii < 3; ii++)
+#pragma unroll
+            for (int jj = 0; jj < 3; jj++) {
+                acc += (0.125 * w[ii] * w[jj] * 0.5) * A.v[ii][jj];
+                acc += (0.125 * w[ii] * w[jj] * 1.0) * B.v[ii][jj];
+                acc += (0.125 * w[ii] * w[jj] * 0.5) * C.v[ii][jj];
+            }
+        p.coarse[cc] = acc;
+        if (p.coarse2) p.coarse2[cc] = acc;
+        A = C;
+        c += 2 * plane;
+        cc += p.gc.plane;
+    }
+}
+
+// ---------------------------------------------------------------------------------
 // residual fused with full-weighting restriction
 // ---------------------------------------------------------------------------------
 // A CTA owns CX x CY coarse columns and marches along coarse z.  Coarse point (X,Y,Z) needs the
@@ -467,6 +537,27 @@ cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
     p.zchunk += p.zchunk & 1;  // even chunks: every chunk starts on the same plane parity
     dim3 grid((npx + PBX - 1) / PBX, (npy + PBY - 1) / PBY, (ze - zb + p.zchunk - 1) / p.zchunk);
     prolong_correct_zmarch<<<grid, dim3(PBX, PBY), 0, cx.stream>>>(p);
+    *handled = true;
+    if (cx.launches) ++*cx.launches;
+    return cudaGetLastError();
+}
+
+// coarse(interior of local coarse planes [zcb, zce)) = full weighting of fine; needs fine planes 2Z-1 .. 2Z+1 of each
+cudaError_t kt_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zcb, int zce, const double* fine, double* coarse,
+                        double* coarse2, bool* handled)
+{
+    *handled = false;
+    if (zce <= zcb) return cudaSuccess;
+    if (gc.nx < 24 || gc.ny < 8) return cudaSuccess;  // tiny levels: the one-thread-per-point kernel
+    int occ = 8;
+    if (cudaError_t e = gs_dev_once(g_restrict_once, &occ,
+                                    [](int* o) { return cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, restrict_zmarch, RBX * RBY, 0); }))
+        return e;
+    RestrictFastP p{gf, gc, zcb, zce, 0, fine, coarse, coarse2};
+    const int tx = (gc.nx + RBX - 1) / RBX, ty = (gc.ny + RBY - 1) / RBY;
+    p.zchunk = cx.tune.wave ? gs_pick_zchunk_waves(cx, tx * ty, zce - zcb, occ, 1, 4, 64, false) : gs_pick_zchunk(cx, tx * ty, zce - zcb, 32);
+    dim3 grid(tx, ty, (zce - zcb + p.zchunk - 1) / p.zchunk);
+    restrict_zmarch<<<grid, dim3(RBX, RBY), 0, cx.stream>>>(p);
     *handled = true;
     if (cx.launches) ++*cx.launches;
     return cudaGetLastError();
