@@ -126,6 +126,7 @@ struct gs_handle {
     size_t stage_count;
     TailRec* tail;        // recorder of the coarse tail (cx.tune.tail_points > 0), made on first use
     int opt_overlap;      // slabs: ghost refresh on a second stream, overlapped with the interior of the operator that needs it
+    int opt_fuse_pc;      // prolongation + correction folded into the first post-smoothing pass (kernels_fused.cu PC)
     int opt_p2p;          // slabs: ghost planes, coarse gather and norm through peer-mapped memory (kernels_comm.cu) instead of NCCL
     std::vector<long long> arena_offs;  // byte offset of every registered array in the arena (index level * GS_LEVEL_ARRAYS + slot; last = newtonF)
     char* arena;          // slabs: every level array lives in ONE allocation, shared with the peers by CUDA IPC
@@ -680,7 +681,18 @@ int do_fas_coarse_rhs(gs_handle* h, int level)
     return GS_OK;
 }
 
-// (mode 1: v_{l+1} -= restV_{l+1};) e = P v_{l+1}; v_l += e   src/cpu/CpuSolver.cpp:121-132
+// mode 1: v_{l+1} -= restV_{l+1}   src/cpu/CpuSolver.cpp:121-125
+int fas_coarse_delta(gs_handle* h, int level)
+{
+    Level& C = h->lev[level + 1];
+    if (h->p.mode != GS_MODE_NONLINEAR) return GS_OK;
+    OpScope t(h, GS_OP_PROLONG, level);
+    CU(ks_axpy(h->cx, C.g, 0, C.g.nzl, C.v, C.restV, -1));
+    C.gv = std::min(C.gv, 1);  // restV carries one current ghost plane
+    return GS_OK;
+}
+
+// e = P v_{l+1}; v_l += e   src/cpu/CpuSolver.cpp:128-132 (after fas_coarse_delta)
 int do_prolong_correct(gs_handle* h, int level)
 {
     Level& F = h->lev[level];
@@ -688,10 +700,6 @@ int do_prolong_correct(gs_handle* h, int level)
     OpScope t(h, GS_OP_PROLONG, level);
     F.pre_valid = 0;
     GS(need_v_halo(h, level + 1, 1));  // the interpolation reads one coarse plane outside the slab
-    if (h->p.mode == GS_MODE_NONLINEAR) {
-        CU(ks_axpy(h->cx, C.g, 0, C.g.nzl, C.v, C.restV, -1));
-        C.gv = std::min(C.gv, 1);  // restV carries one current ghost plane
-    }
     // an odd number of sweeps per cycle would leave v/vtmp swapped; writing the corrected
     // field out of place in that case keeps the buffer parity (and the CUDA graph) fixed
     const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
@@ -700,6 +708,32 @@ int do_prolong_correct(gs_handle* h, int level)
     if (!handled) CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
     if (flip) std::swap(F.v, F.vtmp);
     F.gv = 0;
+    return GS_OK;
+}
+
+// Prolongation + correction folded into the first post-smoothing pass (north_star fusion list; src/cpu/CpuSolver.cpp:128-134):
+// vtmp = S(S(v + P v_{l+1})), the corrected iterate never goes to memory (kernels_fused.cu smooth2u_tma<.., PC>).  *done =
+// false: not applicable here (small level, odd sweep total, slab, option off) and nothing was launched.
+int try_prolong_smooth2(gs_handle* h, int level, bool* done)
+{
+    *done = false;
+    Level& F = h->lev[level];
+    Level& C = h->lev[level + 1];
+    const int km = smoother_km(h);
+    const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
+    if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || h->cx.rec || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
+        partitioned(h, level) || km == KM_NEWTON_EXP)
+        return GS_OK;
+    if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
+    OpScope t(h, GS_OP_SMOOTH, level);
+    bool handled = false;
+    CU(kx_smooth2(h->cx, km, F.ar, F.g, F.ib, F.ie, F.k, F.v, F.vtmp, F.f, smoother_aux(h, level, km), false, false, &handled, C.v, &C.g));
+    if (!handled) return GS_OK;
+    F.pre_valid = 0;
+    h->lvl_sweeps[level] += 2;
+    std::swap(F.v, F.vtmp);
+    F.gv = 0;
+    *done = true;
     return GS_OK;
 }
 
@@ -768,8 +802,11 @@ int enqueue_vcycle_ops(gs_handle* h, int tail, bool host_norm)
         std::swap(L.v, L.vtmp);
     }
     for (int i = last; i > 0; i--) {
-        GS(do_prolong_correct(h, i - 1));
-        GS(do_smooth(h, i - 1, h->p.post));
+        GS(fas_coarse_delta(h, i - 1));
+        bool fused = false;
+        GS(try_prolong_smooth2(h, i - 1, &fused));
+        if (!fused) GS(do_prolong_correct(h, i - 1));
+        GS(do_smooth(h, i - 1, h->p.post - (fused ? 2 : 0)));
         if (i - 1 == tail) GS(tail_end(h));
     }
     GS(do_norm_residual(h));
@@ -1269,6 +1306,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->arena_bytes = 0;
     h->opt_p2p = 1;
     if (const char* e = getenv("GPUSOLVE_P2P")) h->opt_p2p = atoi(e) != 0;
+    h->opt_fuse_pc = 0;
+    if (const char* e = getenv("GPUSOLVE_FUSE_PC")) h->opt_fuse_pc = atoi(e) != 0;
     h->opt_device_stop = 1;
     if (const char* e = getenv("GPUSOLVE_DEVICE_STOP")) h->opt_device_stop = atoi(e) != 0;
     h->d_stop = nullptr;
@@ -1808,6 +1847,7 @@ int gs_prolong_correct(gs_handle* h, int level)
     GS(check_level(h, level));
     GS(check_level(h, level + 1));
     CU(cudaSetDevice(h->device));
+    GS(fas_coarse_delta(h, level));
     return do_prolong_correct(h, level);
 }
 
@@ -1958,6 +1998,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "overlap") h->opt_overlap = value != 0;
     else if (n == "device_stop") h->opt_device_stop = value != 0;
     else if (n == "p2p") h->opt_p2p = value != 0;
+    else if (n == "fuse_pc") h->opt_fuse_pc = value != 0;
     else if (n == "tail_points") h->cx.tune.tail_points = (int)std::max<int64_t>(0, std::min<int64_t>(1 << 20, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;

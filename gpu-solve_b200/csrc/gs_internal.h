@@ -155,9 +155,11 @@ cudaError_t kf_smooth_norm(const LaunchCtx& cx, int km, int ar, const Geom& g, i
 cudaError_t kx_prepare();
 // vout = S(S(vin)) on local planes [zb, ze); needs two valid planes of vin outside the range.  with_norm: also
 // sum of squares of the residual of vin -> cx.norm.result
+// coarse != nullptr: the sweeps start from vin + P(coarse) (prolongation + correction folded into the pass; gc = geometry of
+// the coarse level; needs the coarse planes of fine planes zb-2 .. ze+1; no norm, no vzero)
 cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k,
                        const double* vin, double* vout, const double* f, const double* aux, bool with_norm, bool vzero,
-                       bool* handled);
+                       bool* handled, const double* coarse = nullptr, const Geom* gc = nullptr, bool prepare_pc = false);
 
 // ---- kernels_transfer.cu: tuned grid-transfer kernels (canonical stencil) ----
 cudaError_t kt_prepare();

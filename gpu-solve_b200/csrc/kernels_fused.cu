@@ -45,6 +45,9 @@ struct Fused2P {
     const double* f;
     const double* aux;
     NormBuf nb;
+    // PC kernels: the iterate the sweeps start from is vin + P(coarse) (prolongation + correction folded into the pass)
+    const double* coarse;
+    Geom gc;
 };
 
 template <int TY, int NSTAGE>
@@ -235,10 +238,19 @@ struct S2uCfg {
 
 // VZ: the input iterate is identically zero (first pre-smoothing pass on a coarse level, src/cpu/CpuSolver.cpp:100-101):
 // v is neither zeroed by a memset nor read — the taps are the constant 0.0, same arithmetic, same bits.
-template <int KM, int AR, bool NORM, int TY, bool VZ>
+// PC: prolongation + correction folded into the first post-smoothing pass (src/cpu/CpuSolver.cpp:128-134: interpolate,
+// v += e, jacobi).  The corrected iterate v + P v_c is never written to memory: as plane q+2 of v arrives in the ring,
+// every thread adds e to the box entries it owns (its two rows, plus the outermost rim row for the first / last row pair)
+// IN PLACE in shared memory — two planes ahead of the first sweep, so the split-phase barrier of step q+1 already orders
+// these stores before any neighbour reads them at step q+2 (tests/ring_model.py smooth2_prolong; one plane ahead would
+// race).  e is the closed form of the four interpolation passes (kernels_simple.cu prolong_point, nesting x -> y -> z),
+// marched along z: the thread keeps ax of its coarse rows j and j+1 on the current coarse plane and loads four coarse
+// values per ODD fine plane.  17 + 24 B per point become 25.
+template <int KM, int AR, bool NORM, int TY, bool VZ, bool PC = false>
 __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __grid_constant__ CUtensorMap map_v,
                                                                       const __grid_constant__ CUtensorMap map_f, Fused2P p)
 {
+    static_assert(!(PC && VZ), "a zero iterate is not corrected");
     using Cfg = S2uCfg<TY>;
     constexpr int BW = Cfg::BW, NS = Cfg::NSTAGE;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -263,6 +275,9 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
             return;
         }
+        // PC: the stage was last written through the generic proxy (the in-place correction): order those stores before
+        // the bulk copy that overwrites them
+        if (PC) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
                      "r"((VZ ? 0 : Cfg::V_BYTES) + (has_f ? Cfg::F_BYTES : 0))
                      : "memory");
@@ -314,6 +329,51 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
     const double* xp = KM >= KM_NEWTON_EXP ? p.aux + ca0 + plane : nullptr;  // (x, ya) on plane q
     const int qlo = 1 - (p.g.z0 + z0 - 2), qhi = p.g.nz - (p.g.z0 + z0 - 2);  // planes q inside the interior: qlo <= q <= qhi
 
+    // ---- PC: per-thread state of the interpolation (coarse rows j = ya/2 = yb/2 and j+1, coarse column i = x/2) ----
+    const bool pxodd = x & 1;
+    const int pco = GS_XOFF + min(max(x >> 1, 0), p.gc.X - 2) + (int)p.gc.pitch * min(max(ya >> 1, 0), p.gc.Y - 2);
+    const bool pinx = x >= 1 && x <= p.g.nx;
+    const bool pmA = pinx && ya >= 1 && ya <= p.g.ny, pmB = pinx && yb >= 1 && yb <= p.g.ny;
+    // the rim row nobody owns as a centre: row 0 of the box (y0-2, odd: coarse rows j-1, j) for the first row pair, row
+    // TY+3 (y0+TY+1, even: coarse row j+1) for the last
+    const bool pmR = pinx && (tr == 0 ? (y0 - 2 >= 1) : (tr == LAST_TR && y0 + TY + 1 <= p.g.ny));
+    const int zgq0 = p.g.z0 + z0 - 2;  // global fine plane of q = 0
+    double pcA = 0.0, pcJ = 0.0;       // ax of coarse rows j, j+1 on the current coarse plane
+    auto pc_ax = [&](const double* c) { return pxodd ? 0.5 * __ldg(c) + 0.5 * __ldg(c + 1) : __ldg(c); };
+    auto pc_plane = [&](int kglob) {   // coarse plane (clamped into the local array; clamped values are never used)
+        return p.coarse + (i64)min(max(kglob - p.gc.z0, 0), p.gc.nzl - 1) * p.gc.plane + pco;
+    };
+    // add e to the own entries of plane P, whose (x, ya) entry sits at shared address a
+    auto pc_correct = [&](uint32_t a, int P) {
+        const int zg = zgq0 + P;
+        double eA = pcA, eJ = pcJ, eM = 0.0;  // interpolants on rows j, j+1 (and j-1 for the first row pair)
+        if (zg & 1) {
+            const double* c = pc_plane((zg >> 1) + 1);
+            const double nA = pc_ax(c), nJ = pc_ax(c + p.gc.pitch);
+            eA = 0.5 * pcA + 0.5 * nA;
+            eJ = 0.5 * pcJ + 0.5 * nJ;
+            if (tr == 0 && pmR) {
+                const double* c0 = pc_plane(zg >> 1);
+                eM = 0.5 * pc_ax(c0 - p.gc.pitch) + 0.5 * pcA;                  // ay(k), rows j-1 and j
+                eM = 0.5 * eM + 0.5 * (0.5 * pc_ax(c - p.gc.pitch) + 0.5 * nA);  // ... averaged with ay(k+1)
+            }
+            // (y odd, z odd): 0.5*ay(k) + 0.5*ay(k+1) with ay = 0.5*ax(j) + 0.5*ax(j+1)
+            const double eBo = 0.5 * (0.5 * pcA + 0.5 * pcJ) + 0.5 * (0.5 * nA + 0.5 * nJ);
+            pcA = nA;
+            pcJ = nJ;
+            if (zg >= 1 && zg <= p.g.nz) {
+                if (pmA) sts_f64(a, lds_f64(a) + eA);
+                if (pmB) sts_f64(a + ROW, lds_f64(a + ROW) + eBo);
+                if (pmR) sts_f64(tr == 0 ? a - ROW : a + 2 * ROW, lds_f64(tr == 0 ? a - ROW : a + 2 * ROW) + (tr == 0 ? eM : eJ));
+            }
+        } else if (zg >= 1 && zg <= p.g.nz) {
+            if (tr == 0 && pmR) eM = 0.5 * pc_ax(pc_plane(zg >> 1) - p.gc.pitch) + 0.5 * pcA;
+            if (pmA) sts_f64(a, lds_f64(a) + eA);
+            if (pmB) sts_f64(a + ROW, lds_f64(a + ROW) + (0.5 * eA + 0.5 * eJ));
+            if (pmR) sts_f64(tr == 0 ? a - ROW : a + 2 * ROW, lds_f64(tr == 0 ? a - ROW : a + 2 * ROW) + (tr == 0 ? eM : eJ));
+        }
+    };
+
     double vq[3][2], s1q[3][2], fq[2][2], xq[2][2];
 #pragma unroll
     for (int i = 0; i < 3; i++) s1q[i][0] = s1q[i][1] = 0.0;
@@ -322,6 +382,19 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
     double sq = 0.0;
 #pragma unroll
     for (int i = 0; i < 3; i++) vq[i][0] = vq[i][1] = 0.0;
+    if (PC) {
+        // planes 0, 1, 2 are corrected up front (a CTA barrier orders them); step q then corrects plane q + 2
+        const double* c = pc_plane(zgq0 >> 1);
+        pcA = pc_ax(c);
+        pcJ = pc_ax(c + p.gc.pitch);
+#pragma unroll
+        for (int P = 0; P < 3; P++)
+            if (P <= nzo + 3) {
+                mbar_wait_a(bars + P * 8, 0);
+                pc_correct(tb + P * Cfg::STAGE, P);
+            }
+        __syncthreads();
+    }
     if (!VZ) {
         mbar_wait_a(bars + 0, 0);
         vq[0][0] = lds_f64(tb);
@@ -345,6 +418,15 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
         }
         const uint32_t c = tb + SC * Cfg::STAGE, u = tb + SU * Cfg::STAGE;
         double Ea = 0.0, Wa = 0.0, Sa = 0.0, Eb = 0.0, Wb = 0.0, Nb = 0.0;
+        if (PC) {
+            // plane q+2 (two ahead of the first sweep): wait for it and add e to the own entries.  Plane q+1 was waited
+            // for one step ago, so the wait below on its stage returns at once.
+            if (q + 2 <= nzo + 3) {
+                constexpr int S2 = (K + 2) % NS;
+                mbar_wait_a(bars + S2 * 8, K >= NS - 2 ? par ^ 1u : par);
+                pc_correct(tb + S2 * Cfg::STAGE, q + 2);
+            }
+        }
         if (VZ) {
             mbar_wait_a(bars + SC * 8, par);  // only the f box of plane q
         } else {
@@ -465,15 +547,15 @@ cudaError_t launch_s2(const LaunchCtx& cx, Fused2P p, bool* handled)
     return cudaGetLastError();
 }
 
-template <int KM, int AR, bool NORM, int TY, bool VZ>
+template <int KM, int AR, bool NORM, int TY, bool VZ, bool PC = false>
 cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
 {
     using Cfg = S2uCfg<TY>;
     static DevOnce once;
     int occ = 1;
     cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
-        cudaError_t e = cudaFuncSetAttribute(smooth2u_tma<KM, AR, NORM, TY, VZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, smooth2u_tma<KM, AR, NORM, TY, VZ>, Cfg::THREADS, Cfg::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(smooth2u_tma<KM, AR, NORM, TY, VZ, PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, smooth2u_tma<KM, AR, NORM, TY, VZ, PC>, Cfg::THREADS, Cfg::SMEM);
         return e;
     });
     if (pe != cudaSuccess) return pe;
@@ -493,14 +575,18 @@ cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
     }
     dim3 grid(tx, ty, (planes + p.zchunk - 1) / p.zchunk);
     if (NORM && (size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaSuccess;
-    smooth2u_tma<KM, AR, NORM, TY, VZ><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
+    smooth2u_tma<KM, AR, NORM, TY, VZ, PC><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, mf, p);
     *handled = true;
     return cudaGetLastError();
 }
 
 template <int KM, int AR, bool NORM>
-cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool vzero, bool* handled)
+cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool vzero, bool pc, bool* handled)
 {
+    if (pc) {  // prolongation + correction folded in: the unrolled kernel only, no norm, a real input iterate
+        if (variant == 1 || KM == KM_NEWTON_EXP || NORM || vzero) return cudaSuccess;
+        return launch_s2u<KM, AR, false, 12, false, true>(cx, p, handled);
+    }
     // the unrolled kernel spills heavily with exp() of the Newton iterate in the loop (KM_NEWTON_EXP, only reached
     // with the precomputed-coefficient path switched off): that mode keeps the rolled kernel
     if (variant == 1 || KM == KM_NEWTON_EXP) return vzero ? cudaSuccess : launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
@@ -518,21 +604,23 @@ cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool
 // planes of vin and one of f (and aux) outside [zb, ze).  vzero: vin is to be taken as identically zero and is not read
 // (handled only by the unrolled kernel in modes 0 and 2 without norm).
 cudaError_t kx_smooth2(const LaunchCtx& cx, int km, int ar, const Geom& g, int zb, int ze, const PointK& k, const double* vin,
-                       double* vout, const double* f, const double* aux, bool with_norm, bool vzero, bool* handled)
+                       double* vout, const double* f, const double* aux, bool with_norm, bool vzero, bool* handled, const double* coarse,
+                       const Geom* gc, bool prepare_pc)
 {
     *handled = false;
     if (vin) {
         if (ze <= zb || cx.tune.fuse2 == 0) return cudaSuccess;
         if (g.nx < cx.tune.fuse2_min_n || g.ny < 16 || ze - zb < 16) return cudaSuccess;  // small levels: single sweeps
     }
-    Fused2P p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm};
+    Fused2P p{g, k, zb, ze, 0, vin, vout, f, aux, cx.norm, coarse, gc ? *gc : Geom{}};
+    const bool pc = coarse != nullptr || prepare_pc;
     p.zchunk = cx.tune.zchunk2 > 0 ? cx.tune.zchunk2 : 128;
     const int lo = vin ? cx.tune.fuse2 - 1 : 0, hi = vin ? cx.tune.fuse2 - 1 : 1;
     cudaError_t e = cudaSuccess;
     for (int var = lo; var <= hi && e == cudaSuccess; var++) {
 #define CALL(KMV)                                                                    \
-    AR_SWITCH(ar, e = with_norm ? (dispatch_s2<KMV, ARV, true>(cx, p, var, vzero, handled)) \
-                                : (dispatch_s2<KMV, ARV, false>(cx, p, var, vzero, handled)))
+    AR_SWITCH(ar, e = with_norm ? (dispatch_s2<KMV, ARV, true>(cx, p, var, vzero, pc, handled)) \
+                                : (dispatch_s2<KMV, ARV, false>(cx, p, var, vzero, pc, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;
         case KM_NONLINEAR: CALL(KM_NONLINEAR); break;
@@ -556,6 +644,8 @@ cudaError_t kx_prepare()
         for (int pw = 0; pw < 8 && e == cudaSuccess; pw++)
             for (int nm = 0; nm < 2 && e == cudaSuccess; nm++)
                 for (int vz = 0; vz < 2 && e == cudaSuccess; vz++)
-                    e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, vz != 0, &handled);
+                    for (int pc = 0; pc < 2 && e == cudaSuccess; pc++)
+                        e = kx_smooth2(cx, km, pw, g, 0, 0, k, nullptr, nullptr, nullptr, nullptr, nm != 0, vz != 0, &handled, nullptr, nullptr,
+                                       pc != 0);
     return e;
 }

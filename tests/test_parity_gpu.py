@@ -331,6 +331,45 @@ def test_device_side_stopping_equals_the_host_loop(name, gs, golden):
         assert res[0][1] == g["inner_cycles"]
 
 
+@pytest.mark.parametrize("mode,n,pre,post", [
+    (0, 127, 2, 2), (0, 255, 2, 2), (0, (131, 97, 63), 4, 4), (0, (200, 150, 300), 1, 3), (0, 120, 2, 2), (0, 513, 2, 2),
+    (1, (121, 64, 70), 4, 2), (1, 191, 2, 2), (2, (100, 90, 47), 2, 4), (2, 191, 3, 3),
+])
+def test_prolongation_folded_into_the_post_smoother_keeps_the_bits(gs, mode, n, pre, post):
+    """fuse_pc: prolongation + correction + the first two post-smoothing sweeps as ONE pass (kernels_fused.cu smooth2u_tma<.., PC>;
+    src/cpu/CpuSolver.cpp:128-134) — the corrected iterate only ever exists in shared memory.  Same per-point arithmetic in
+    the same order, so the fields must equal the separate passes bit for bit (also with exp(): identical instructions), back to
+    back, with and without the graph, and one launch per level fewer."""
+    kw = dict(n=n, mode=mode, pre=pre, post=post, maxiter=1, tol=1e-30)
+    ref = CudaBackend(gs, kernels=1, graph=0, **kw)
+    ref.set_option("fuse_pc", 0)
+    v0 = seeded_field(ref.shape(0), 21)
+    field = NEWTONV if mode == 2 else V
+
+    def run(b):
+        b.set(0, V, v0)
+        if mode == 2:
+            b.set(0, NEWTONV, v0)
+            return [b.newton_step()[0] for _ in range(2)], b.get(0, field)
+        return [b.vcycle() for _ in range(3)], b.get(0, field)
+
+    rn, rv = run(ref)
+    l0 = ref.launches
+    run(ref)
+    per_run = ref.launches - l0
+    ref.close()
+    for graph in (0, 1):
+        b = CudaBackend(gs, kernels=1, graph=graph, **kw)
+        b.set_option("fuse_pc", 1)
+        for rep in range(2):
+            l0 = b.launches
+            norms, v = run(b)
+            assert digest(v) == digest(rv), f"graph {graph} rep {rep}: fields differ (max rel {rel_err(v, rv):.3e})"
+            assert norms == rn
+            assert b.launches - l0 < per_run, "no prolongation launch was folded away"
+        b.close()
+
+
 # Variants written while no GPU time was left (DESIGN.md section 9): default off, and so are their tests, which a
 # round-end run must not trip over.  GPUSOLVE_TEST_PREPARED=1 (tools/gpu_round.sh sets it) runs them.
 prepared = pytest.mark.skipif(os.environ.get("GPUSOLVE_TEST_PREPARED") != "1",
