@@ -10,7 +10,7 @@ nproc > $out/${tag}_nproc.txt; free -g >> $out/${tag}_nproc.txt; lscpu | head -2
 GPUSOLVE_TEST_PREPARED=1 timeout 900 python -m pytest tests -m gpu -q --durations=15 > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $out/${tag}_pytest_gpu.log
 timeout 400 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench exit $?" >> $out/${tag}_bench.err
 timeout 200 python bench.py --impl reference > $out/${tag}_bench_ref.json 2> $out/${tag}_bench_ref.err
-for cfg in "" "GPUSOLVE_TAIL_POINTS=4096" "GPUSOLVE_TAIL_POINTS=40000" "GPUSOLVE_RR_VARIANT=2" "GPUSOLVE_TAIL_POINTS=4096 GPUSOLVE_RR_VARIANT=2"; do
+for cfg in "" "GPUSOLVE_FUSE_PC=1" "GPUSOLVE_TAIL_POINTS=4096" "GPUSOLVE_TAIL_POINTS=40000" "GPUSOLVE_RR_VARIANT=2" "GPUSOLVE_TAIL_POINTS=4096 GPUSOLVE_RR_VARIANT=2 GPUSOLVE_FUSE_PC=1"; do
     name=$(echo "${cfg:-default}" | tr ' =' '__')
     env $cfg timeout 100 python bench.py --steps 30 --warmup 5 --no-cpu --no-e2e --no-extras > $out/${tag}_ab_${name}.json 2> $out/${tag}_ab_${name}.err
 done
@@ -21,6 +21,23 @@ for n in 63 127 255; do
     done
 done
 timeout 100 python tools/profile_levels.py > $out/${tag}_levels.txt 2>&1
+timeout 100 python tools/profile_levels.py --opt fuse_pc=1 > $out/${tag}_levels_pc.txt 2>&1
+cat > /tmp/skew.conf <<'EOC'
+5
+1e-30
+511 511 511
+0
+2
+2
+0.8
+1.0
+6 -1.1 -0.9 -1.2 -0.8 -1.3 -0.7
+0 0 1 0 -1 0 0
+0 0 0 -1 0 1 0
+0 1 0 0 0 0 -1
+EOC
+GPUSOLVE_TIMERS=1 timeout 100 gpu-solve_b200/bin/GpuSolve-cuda /tmp/skew.conf > $out/${tag}_skew511.txt 2>&1
+GPUSOLVE_TIMERS=1 GPUSOLVE_KERNELS=0 timeout 100 gpu-solve_b200/bin/GpuSolve-cuda /tmp/skew.conf > $out/${tag}_skew511_simple.txt 2>&1
 timeout 100 python tools/profile_levels.py --mode 1 > $out/${tag}_levels_mode1.txt 2>&1
 timeout 100 python tools/profile_levels.py --mode 2 --pre 3 --post 3 > $out/${tag}_levels_mode2.txt 2>&1
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict|fas_rhs|restrict_simple' -c 10 \
