@@ -722,10 +722,17 @@ int try_prolong_smooth2(gs_handle* h, int level, bool* done)
     const int km = smoother_km(h);
     const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
     if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || h->cx.rec || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
-        partitioned(h, level) || km == KM_NEWTON_EXP)
+        km == KM_NEWTON_EXP)
         return GS_OK;
+    if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16) return GS_OK;  // kx_smooth2 would decline
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     OpScope t(h, GS_OP_SMOOTH, level);
+    // Slabs: the pass needs v + e on two planes outside the slab.  The uncorrected v ghosts are normally still current (the
+    // residual+restriction on the way down refreshed them and v has not changed since); e on the ghost planes comes from
+    // the coarse iterate one plane below and two planes above the coarse slab.  So the only exchange of the whole
+    // prolongation + first post-smoothing pass is a two-plane refresh of the COARSE level (a quarter of the fine volume).
+    GS(need_v_halo(h, level, 2));
+    GS(need_v_halo(h, level + 1, 2));
     bool handled = false;
     CU(kx_smooth2(h->cx, km, F.ar, F.g, F.ib, F.ie, F.k, F.v, F.vtmp, F.f, smoother_aux(h, level, km), false, false, &handled, C.v, &C.g));
     if (!handled) return GS_OK;
