@@ -152,6 +152,51 @@ GS_HD double jacobi_update(double vc, double r, double den, const PointK& k)
     return vc + k.omega * (r / den);
 }
 
+// ---------------------------------------------------------------------------------
+// z-marched trilinear interpolation of one x column for the fused prolongation + smoother pass (kernels_fused.cu PC)
+// ---------------------------------------------------------------------------------
+// CpuSolver::interpolate in closed form (kernels_simple.cu prolong_point): e(X,Y,Z) = avg_z(avg_y(avg_x(C))) with
+// avg = 0.5*a + 0.5*b on odd indices and the identity on even ones, nesting x -> y -> z.  For a thread that owns the fine
+// rows Y (even) and Y+1 at column X and marches along z, everything it needs on a coarse plane k are the x-interpolants
+// ax of coarse rows j = Y/2 and j+1; they are carried from plane to plane, so only ODD fine planes load new coarse
+// values.  `ld(k, row)` returns ax of coarse row j+row (row in {-1, 0, 1}) on GLOBAL coarse plane k.  Results per plane:
+//   eA  row Y   (even)            eB  row Y+1 (odd)
+//   eJ  row Y+2 (even: the rim row above the last row pair of a tile)
+//   eM  row Y-1 (odd:  the rim row below the first row pair; only evaluated when want_m)
+// Same operations in the same order as prolong_point, hence the same bits (tests/test_pc_host.py checks every point).
+struct PcInterp {
+    double a, j;  // ax(row j), ax(row j+1) on coarse plane zg >> 1 of the plane that comes next
+    template <class LD>
+    GS_HD void init(int zg0, LD&& ld)
+    {
+        a = ld(zg0 >> 1, 0);
+        j = ld(zg0 >> 1, 1);
+    }
+    template <class LD>
+    GS_HD void step(int zg, bool want_m, LD&& ld, double& eA, double& eB, double& eJ, double& eM)
+    {
+        eM = 0.0;
+        if (zg & 1) {
+            const int k1 = (zg >> 1) + 1;
+            const double nA = ld(k1, 0), nJ = ld(k1, 1);
+            eA = 0.5 * a + 0.5 * nA;
+            eJ = 0.5 * j + 0.5 * nJ;
+            eB = 0.5 * (0.5 * a + 0.5 * j) + 0.5 * (0.5 * nA + 0.5 * nJ);
+            if (want_m) {
+                const double m0 = 0.5 * ld(zg >> 1, -1) + 0.5 * a, m1 = 0.5 * ld(k1, -1) + 0.5 * nA;
+                eM = 0.5 * m0 + 0.5 * m1;
+            }
+            a = nA;
+            j = nJ;
+        } else {
+            eA = a;
+            eJ = j;
+            eB = 0.5 * a + 0.5 * j;
+            if (want_m) eM = 0.5 * ld(zg >> 1, -1) + 0.5 * a;
+        }
+    }
+};
+
 // canonical tap order C,+x,-x,+y,-y,+z,-z (config order of the axis-aligned stencil)
 template <int AR>
 __device__ __forceinline__ double canon_tap_sum(double C, double E, double W, double N, double S, double U, double D, const PointK& k)

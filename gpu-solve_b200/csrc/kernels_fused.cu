@@ -338,39 +338,24 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
     // TY+3 (y0+TY+1, even: coarse row j+1) for the last
     const bool pmR = pinx && (tr == 0 ? (y0 - 2 >= 1) : (tr == LAST_TR && y0 + TY + 1 <= p.g.ny));
     const int zgq0 = p.g.z0 + z0 - 2;  // global fine plane of q = 0
-    double pcA = 0.0, pcJ = 0.0;       // ax of coarse rows j, j+1 on the current coarse plane
-    auto pc_ax = [&](const double* c) { return pxodd ? 0.5 * __ldg(c) + 0.5 * __ldg(c + 1) : __ldg(c); };
-    auto pc_plane = [&](int kglob) {   // coarse plane (clamped into the local array; clamped values are never used)
-        return p.coarse + (i64)min(max(kglob - p.gc.z0, 0), p.gc.nzl - 1) * p.gc.plane + pco;
+    PcInterp pci{0.0, 0.0};
+    // ax of coarse row j + row on GLOBAL coarse plane k (clamped into the local array; clamped values are never used)
+    auto pc_ld = [&](int k, int row) {
+        const double* c = p.coarse + (i64)min(max(k - p.gc.z0, 0), p.gc.nzl - 1) * p.gc.plane + pco + row * (int)p.gc.pitch;
+        return pxodd ? 0.5 * __ldg(c) + 0.5 * __ldg(c + 1) : __ldg(c);
     };
     // add e to the own entries of plane P, whose (x, ya) entry sits at shared address a
     auto pc_correct = [&](uint32_t a, int P) {
         const int zg = zgq0 + P;
-        double eA = pcA, eJ = pcJ, eM = 0.0;  // interpolants on rows j, j+1 (and j-1 for the first row pair)
-        if (zg & 1) {
-            const double* c = pc_plane((zg >> 1) + 1);
-            const double nA = pc_ax(c), nJ = pc_ax(c + p.gc.pitch);
-            eA = 0.5 * pcA + 0.5 * nA;
-            eJ = 0.5 * pcJ + 0.5 * nJ;
-            if (tr == 0 && pmR) {
-                const double* c0 = pc_plane(zg >> 1);
-                eM = 0.5 * pc_ax(c0 - p.gc.pitch) + 0.5 * pcA;                  // ay(k), rows j-1 and j
-                eM = 0.5 * eM + 0.5 * (0.5 * pc_ax(c - p.gc.pitch) + 0.5 * nA);  // ... averaged with ay(k+1)
-            }
-            // (y odd, z odd): 0.5*ay(k) + 0.5*ay(k+1) with ay = 0.5*ax(j) + 0.5*ax(j+1)
-            const double eBo = 0.5 * (0.5 * pcA + 0.5 * pcJ) + 0.5 * (0.5 * nA + 0.5 * nJ);
-            pcA = nA;
-            pcJ = nJ;
-            if (zg >= 1 && zg <= p.g.nz) {
-                if (pmA) sts_f64(a, lds_f64(a) + eA);
-                if (pmB) sts_f64(a + ROW, lds_f64(a + ROW) + eBo);
-                if (pmR) sts_f64(tr == 0 ? a - ROW : a + 2 * ROW, lds_f64(tr == 0 ? a - ROW : a + 2 * ROW) + (tr == 0 ? eM : eJ));
-            }
-        } else if (zg >= 1 && zg <= p.g.nz) {
-            if (tr == 0 && pmR) eM = 0.5 * pc_ax(pc_plane(zg >> 1) - p.gc.pitch) + 0.5 * pcA;
+        double eA, eB, eJ, eM;
+        pci.step(zg, tr == 0 && pmR, pc_ld, eA, eB, eJ, eM);
+        if (zg >= 1 && zg <= p.g.nz) {
             if (pmA) sts_f64(a, lds_f64(a) + eA);
-            if (pmB) sts_f64(a + ROW, lds_f64(a + ROW) + (0.5 * eA + 0.5 * eJ));
-            if (pmR) sts_f64(tr == 0 ? a - ROW : a + 2 * ROW, lds_f64(tr == 0 ? a - ROW : a + 2 * ROW) + (tr == 0 ? eM : eJ));
+            if (pmB) sts_f64(a + ROW, lds_f64(a + ROW) + eB);
+            if (pmR) {
+                const uint32_t r = tr == 0 ? a - ROW : a + 2 * ROW;
+                sts_f64(r, lds_f64(r) + (tr == 0 ? eM : eJ));
+            }
         }
     };
 
@@ -384,9 +369,7 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
     for (int i = 0; i < 3; i++) vq[i][0] = vq[i][1] = 0.0;
     if (PC) {
         // planes 0, 1, 2 are corrected up front (a CTA barrier orders them); step q then corrects plane q + 2
-        const double* c = pc_plane(zgq0 >> 1);
-        pcA = pc_ax(c);
-        pcJ = pc_ax(c + p.gc.pitch);
+        pci.init(zgq0, pc_ld);
 #pragma unroll
         for (int P = 0; P < 3; P++)
             if (P <= nzo + 3) {
