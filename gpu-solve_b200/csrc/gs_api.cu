@@ -1202,7 +1202,13 @@ int newton_compF(gs_handle* h, double* norm)
     L.pre_valid = false;  // f changes
     {
         OpScope t(h, GS_OP_RESIDUAL, 0);
-        CU(ks_newton_F(h->cx, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.newtonV, h->newtonF, L.f));
+        // F(newtonV) = newtonF - (A newtonV / h^2 + gamma newtonV e^newtonV) is the mode-1 residual of the pair (newtonV,
+        // newtonF), expression for expression (gs_device.cuh finish_residual<KM_NONLINEAR> vs kernels_simple.cu
+        // newton_F_simple): the tuned residual kernel computes it, stores it as f and reduces its norm
+        bool handled = false;
+        if (h->opt_kernels && !h->cx.rec)
+            CU(kf_residual(h->cx, KM_NONLINEAR, L.ar, L.g, L.ib, L.ie, L.k, L.newtonV, h->newtonF, nullptr, L.f, &handled, gen_offsets(h)));
+        if (!handled) CU(ks_newton_F(h->cx, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.newtonV, h->newtonF, L.f));
         GS(exchange_halo(h, 0, L.f, 1));  // the residual+restriction of a slab reads f one plane outside it
     }
     GS(norm_to_host(h, 0));
