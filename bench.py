@@ -489,15 +489,25 @@ def main():
     sm_n = ll[0].get("smooth", 0.0)
     launch_ms = lm[0].get("smooth", 0.0) / max(sm_n, 1e-9)
     per_launch = sweeps0 / max(sm_n, 1e-9)
-    pass_bytes = 24.0 * P[0] / world                      # read v, read f, write v'' once per launch (this rank's slab)
+    # the post-smoothing pass may carry the prolongation + correction (fuse_pc): then it also reads the coarse iterate
+    # (1 B per fine point) and there is no separate prolongation launch on level 0
+    fused_pc = per_launch > 1.5 and ll[0].get("prolong", 0.0) == 0.0 and len(P) > 1
+    pass_bytes = (25.0 if fused_pc else 24.0) * P[0] / world   # read v, read f, write v'' once per launch (this rank's slab)
     achieved = pass_bytes / (launch_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath) and n == REF_GRID:
         with open(tpath) as f:
-            traffic = json.load(f).get(("smooth2_n%d" if per_launch > 1.5 else "smooth_n%d") % n[0], None)
-    kname = ("smooth2u_tma: two damped-Jacobi sweeps per pass (temporal blocking, z-march unrolled over the ring period)" if per_launch > 1.5
+            traffic = json.load(f).get(("smooth2pc_n%d" if fused_pc else "smooth2_n%d" if per_launch > 1.5 else "smooth_n%d") % n[0], None)
+    kname = ("smooth2u_tma<PC>: prolongation + correction + two damped-Jacobi sweeps in one pass" if fused_pc else
+             "smooth2u_tma: two damped-Jacobi sweeps per pass (temporal blocking, z-march unrolled over the ring period)" if per_launch > 1.5
              else "stencil_tma: one damped-Jacobi sweep per pass")
+    # the other level-0 two-sweep pass of a cycle: the one that also reduces the residual norm (GS_OP_RESIDUAL)
+    nr_n = ll[0].get("residual", 0.0)
+    norm_ms = lm[0].get("residual", 0.0) / max(nr_n, 1e-9)
+    norm_pass = {"kernel": "smooth2u_tma<NORM>: the cycle's residual norm + the next cycle's two pre-smoothing sweeps", "ms_per_launch": norm_ms,
+                 "achieved": 24.0 * P[0] / world / max(norm_ms * 1e-3, 1e-12) / 1e9,
+                 "frac": 24.0 * P[0] / world / max(norm_ms * 1e-3, 1e-12) / 1e9 / peak} if nr_n else None
     roofline = {"bound": "hbm", "kernel": "fine-level smoother (level 0, inside the V-cycle) - " + kname, "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": pass_bytes, "ms_per_launch": launch_ms, "sweeps_per_launch": per_launch,
@@ -505,9 +515,11 @@ def main():
                 "lup_equivalent_gbs": 24.0 * P[0] / world * per_launch / (launch_ms * 1e-3) / 1e9,
                 "dram_gbs": (traffic / (launch_ms * 1e-3) / 1e9) if traffic else None,
                 "dram_frac": (traffic / (launch_ms * 1e-3) / 1e9 / peak) if traffic else None,
-                "note": "achieved = compulsory bytes of ONE PASS (v and f read, v'' written once: 24 B per point of this GPU's slab) / "
-                        "average launch time, CUDA events inside the V-cycle; frac is a bandwidth fraction.  The pass applies "
-                        "sweeps_per_launch Jacobi sweeps: glups and lup_equivalent_gbs (24 B per lattice UPDATE, SURVEY 8d) carry that"}
+                "norm_pass": norm_pass,
+                "note": "achieved = compulsory bytes of ONE PASS (v and f read, v'' written once: 24 B per point of this GPU's slab, 25 when "
+                        "the pass also carries the prolongation) / average launch time, CUDA events inside the V-cycle; frac is a bandwidth "
+                        "fraction.  The pass applies sweeps_per_launch Jacobi sweeps: glups and lup_equivalent_gbs (24 B per lattice "
+                        "UPDATE, SURVEY 8d) carry that"}
     vbytes = vcycle_algorithmic_bytes(n, pre, post)
     launched_bytes = pass_level_bytes(n, 0, ll)
 
@@ -570,63 +582,66 @@ def main():
                                      "note": "same 1023^3 grid on N GPUs vs on GPU 0 alone in this run (CUDA events, max over ranks)"}
         # ---- BASELINE.json configs[2], [3] at 513^3 and the shipped config at 129^3, one GPU ----
         if world == 1:
-            extras["modes"] = {}
-            for mode, (mpre, mpost) in ((1, (2, 2)), (2, (3, 3))):
-                s = job.solver(REF_GRID, mode, mpre, mpost)
-                if mode == 2:
-                    s.newton_step()      # a realistic Newton iterate on every level
-                ms, _, ml = job.time_cycles(s, 10, 3)
-                pop, mll, mlm, msw = per_level_profile(s, 5)
-                s.close()
-                sweep = 32 if mode == 2 else 24
-                spn = mll[0].get("smooth", 0.0)
-                sp_ms = mlm[0].get("smooth", 0.0) / max(spn, 1e-9)
-                lb = pass_level_bytes(REF_GRID, mode, mll)
-                extras["modes"][str(mode)] = {
-                    "config": f"mode {mode} ({'FAS, gamma=1' if mode == 1 else 'Newton-linearised, precomputed coefficient'}), 513^3, V({mpre},{mpost})",
-                    "ms_per_cycle": ms, "vcycles_per_s": 1e3 / ms, "launches_per_cycle": ml / 10,
-                    "dominant_kernel": "smooth2u_tma<%s> level 0" % ("KM_NONLINEAR" if mode == 1 else "KM_NEWTON_COEF"),
-                    "pass_ms": sp_ms, "pass_bytes": sweep * P[0], "pass_frac_of_hbm_peak": sweep * P[0] / (sp_ms * 1e-3) / 1e9 / peak,
-                    "sweeps_per_pass": msw / max(spn, 1e-9), "glups": msw * P[0] / max(mlm[0].get("smooth", 1e-9) * 1e-3, 1e-12) / 1e9,
-                    "vcycle_pass_level_bytes": lb, "vcycle_frac_of_peak": lb / (ms * 1e-3) / 1e9 / peak, "per_operator": pop,
-                    "binds": ("fp64 pipe (exp + divide per point per sweep; ncu: profiles/r02_ncu_modes_summary.txt)" if mode == 1 else
-                              "HBM and fp64 pipe together (divide per point per sweep, 32 B per point; ncu: profiles/r02_ncu_modes_summary.txt)")}
-            # the shipped examples/data-2nd_order.conf (BASELINE configs[0]): Newton, 127^3, V(3,3) — ms per Newton iteration
-            p = gs.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5)
-            s = gs.GpuSolve(p, device=job.local)
-            s.newton_step()
-            s.synchronize()
-            t0 = time.perf_counter()
-            inner = 0
-            for _ in range(3):
-                inner += s.newton_step()[1]
-            s.synchronize()
-            gpu_ms = (time.perf_counter() - t0) / 3 * 1e3
-            s.close()
-            small = {"n": 127, "mode": 2, "pre": 3, "post": 3, "ms_per_newton_iter": gpu_ms, "inner_cycles_per_iter": inner / 3,
-                     "note": "examples/data-2nd_order.conf as shipped; wall clock over 3 Newton iterations after one warm-up (includes the host's "
-                             "norm read-backs)"}
-            if not args.no_cpu:
-                orc, kind = cpu_oracle()
-                o = orc.Oracle(orc.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5), kind)
-                o.set_threads(os.cpu_count())
-                o.newton_begin()
-                import numpy as _np
+          try:
+              extras["modes"] = {}
+              for mode, (mpre, mpost) in ((1, (2, 2)), (2, (3, 3))):
+                  s = job.solver(REF_GRID, mode, mpre, mpost)
+                  if mode == 2:
+                      s.newton_step()      # a realistic Newton iterate on every level
+                  ms, _, ml = job.time_cycles(s, 10, 3)
+                  pop, mll, mlm, msw = per_level_profile(s, 5)
+                  s.close()
+                  sweep = 32 if mode == 2 else 24
+                  spn = mll[0].get("smooth", 0.0)
+                  sp_ms = mlm[0].get("smooth", 0.0) / max(spn, 1e-9)
+                  lb = pass_level_bytes(REF_GRID, mode, mll)
+                  extras["modes"][str(mode)] = {
+                      "config": f"mode {mode} ({'FAS, gamma=1' if mode == 1 else 'Newton-linearised, precomputed coefficient'}), 513^3, V({mpre},{mpost})",
+                      "ms_per_cycle": ms, "vcycles_per_s": 1e3 / ms, "launches_per_cycle": ml / 10,
+                      "dominant_kernel": "smooth2u_tma<%s> level 0" % ("KM_NONLINEAR" if mode == 1 else "KM_NEWTON_COEF"),
+                      "pass_ms": sp_ms, "pass_bytes": sweep * P[0], "pass_frac_of_hbm_peak": sweep * P[0] / (sp_ms * 1e-3) / 1e9 / peak,
+                      "sweeps_per_pass": msw / max(spn, 1e-9), "glups": msw * P[0] / max(mlm[0].get("smooth", 1e-9) * 1e-3, 1e-12) / 1e9,
+                      "vcycle_pass_level_bytes": lb, "vcycle_frac_of_peak": lb / (ms * 1e-3) / 1e9 / peak, "per_operator": pop,
+                      "binds": ("fp64 pipe (exp + divide per point per sweep; ncu: profiles/r02_ncu_modes_summary.txt)" if mode == 1 else
+                                "HBM and fp64 pipe together (divide per point per sweep, 32 B per point; ncu: profiles/r02_ncu_modes_summary.txt)")}
+              # the shipped examples/data-2nd_order.conf (BASELINE configs[0]): Newton, 127^3, V(3,3) — ms per Newton iteration
+              p = gs.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5)
+              s = gs.GpuSolve(p, device=job.local)
+              s.newton_step()
+              s.synchronize()
+              t0 = time.perf_counter()
+              inner = 0
+              for _ in range(3):
+                  inner += s.newton_step()[1]
+              s.synchronize()
+              gpu_ms = (time.perf_counter() - t0) / 3 * 1e3
+              s.close()
+              small = {"n": 127, "mode": 2, "pre": 3, "post": 3, "ms_per_newton_iter": gpu_ms, "inner_cycles_per_iter": inner / 3,
+                       "note": "examples/data-2nd_order.conf as shipped; wall clock over 3 Newton iterations after one warm-up (includes the host's "
+                               "norm read-backs)"}
+              if not args.no_cpu:
+                  orc, kind = cpu_oracle()
+                  o = orc.Oracle(orc.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5), kind)
+                  o.set_threads(os.cpu_count())
+                  o.newton_begin()
+                  import numpy as _np
 
-                def cpu_step():
-                    o.newton_compF()
-                    o.set(0, orc.V, _np.zeros(o.shape(0)))
-                    c = o.newton_find_error()
-                    o.newton_compF()
-                    return c
-                cpu_step()
-                t0 = time.perf_counter()
-                cin = sum(cpu_step() for _ in range(3))
-                small["cpu_ms_per_newton_iter"] = (time.perf_counter() - t0) / 3 * 1e3
-                small["cpu_inner_cycles_per_iter"] = cin / 3
-                small["cpu_kind"], small["cpu_cores"] = kind, os.cpu_count()
-                o.close()
-            extras["small"] = small
+                  def cpu_step():
+                      o.newton_compF()
+                      o.set(0, orc.V, _np.zeros(o.shape(0)))
+                      c = o.newton_find_error()
+                      o.newton_compF()
+                      return c
+                  cpu_step()
+                  t0 = time.perf_counter()
+                  cin = sum(cpu_step() for _ in range(3))
+                  small["cpu_ms_per_newton_iter"] = (time.perf_counter() - t0) / 3 * 1e3
+                  small["cpu_inner_cycles_per_iter"] = cin / 3
+                  small["cpu_kind"], small["cpu_cores"] = kind, os.cpu_count()
+                  o.close()
+              extras["small"] = small
+          except Exception as ex:  # a sub-record must never cost the line
+            extras["extras_error"] = repr(ex)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
