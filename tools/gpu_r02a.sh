@@ -40,8 +40,15 @@ GPUSOLVE_TIMERS=1 timeout 100 gpu-solve_b200/bin/GpuSolve-cuda /tmp/skew.conf > 
 GPUSOLVE_TIMERS=1 GPUSOLVE_KERNELS=0 timeout 100 gpu-solve_b200/bin/GpuSolve-cuda /tmp/skew.conf > $out/${tag}_skew511_simple.txt 2>&1
 timeout 100 python tools/profile_levels.py --mode 1 > $out/${tag}_levels_mode1.txt 2>&1
 timeout 100 python tools/profile_levels.py --mode 2 --pre 3 --post 3 > $out/${tag}_levels_mode2.txt 2>&1
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict|fas_rhs|restrict_simple' -c 10 \
-    -o $out/${tag}_mode1 -f python tools/one_cycle.py --n 511 --mode 1 > $out/${tag}_ncu_mode1.log 2>&1
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:'smooth2|resid_restrict|stencil_tma' -c 8 \
-    -o $out/${tag}_mode2 -f python tools/one_cycle.py --n 511 --mode 2 --pre 3 --post 3 --no-newton-step > $out/${tag}_ncu_mode2.log 2>&1
+# ncu: raw counters only, exported to CSV on the box (the .ncu-rep files would exceed the 64 MiB that travel back)
+timeout 300 ncu --set full --clock-control none -k regex:'smooth2|resid_restrict|fas_rhs|restrict_zmarch|stencil_tma' -c 8 \
+    -o /tmp/${tag}_mode1 -f python tools/one_cycle.py --n 511 --mode 1 > $out/${tag}_ncu_mode1.log 2>&1
+ncu -i /tmp/${tag}_mode1.ncu-rep --page raw --csv > $out/${tag}_ncu_mode1_raw.csv 2>/dev/null
+timeout 300 ncu --set full --clock-control none -k regex:'smooth2|resid_restrict|stencil_tma' -c 8 \
+    -o /tmp/${tag}_mode2 -f python tools/one_cycle.py --n 511 --mode 2 --pre 3 --post 3 --no-newton-step > $out/${tag}_ncu_mode2.log 2>&1
+ncu -i /tmp/${tag}_mode2.ncu-rep --page raw --csv > $out/${tag}_ncu_mode2_raw.csv 2>/dev/null
+timeout 300 ncu --set full --clock-control none -k regex:'smooth2|resid_restrict|prolong' -c 8 \
+    -o /tmp/${tag}_mode0 -f python tools/one_cycle.py --n 511 --mode 0 --opt fuse_pc=1 > $out/${tag}_ncu_mode0.log 2>&1
+ncu -i /tmp/${tag}_mode0.ncu-rep --page raw --csv > $out/${tag}_ncu_mode0_raw.csv 2>/dev/null
+du -sh $out > $out/${tag}_du.txt
 echo done
