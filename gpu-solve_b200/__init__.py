@@ -92,7 +92,6 @@ SIGNATURES = {
     "gs_destroy": (_i, [_vp]),
     "gs_partition": (_i, [C.POINTER(Params), _i, _i, _i, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_i)]),
     "gs_plan_zchunk": (_i, [_i, _i, _i, _i, _i, _i, _i, _i]),
-    "gs_plan_tail": (_i, [C.POINTER(Params), C.c_int64]),
     "gs_num_levels": (_i, [_vp]),
     "gs_get_level_info": (_i, [_vp, _i, C.POINTER(_u64 * 3), _dp]),
     "gs_get_field": (_i, [_vp, _i, _i, _vp, _i]),
@@ -158,11 +157,6 @@ def plan_zchunk(tiles, planes, sm_count=148, ctas_per_sm=2, overhead=6, min_chun
     if rc < 0:
         _check(rc)
     return rc
-
-
-def plan_tail(p, tail_points):
-    """first level the coarse tail would start at (-1: none); pure host arithmetic"""
-    return load().gs_plan_tail(C.byref(p), int(tail_points))
 
 
 def comm_unique_id():

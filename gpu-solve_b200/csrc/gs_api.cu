@@ -124,7 +124,6 @@ struct gs_handle {
     int replicated_from;
     double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
     size_t stage_count;
-    TailRec* tail;        // recorder of the coarse tail (cx.tune.tail_points > 0), made on first use
     int opt_overlap;      // slabs: ghost refresh on a second stream, overlapped with the interior of the operator that needs it
     int opt_fuse_pc;      // prolongation + correction folded into the first post-smoothing pass (kernels_fused.cu PC)
     int opt_p2p;          // slabs: ghost planes, coarse gather and norm through peer-mapped memory (kernels_comm.cu) instead of NCCL
@@ -443,7 +442,7 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     }
     L.pre_valid = 0;
     const double* aux = smoother_aux(h, level, km);
-    const bool tuned1 = h->opt_kernels && !h->cx.rec;  // the tail records the one-thread-per-point operators
+    const bool tuned1 = h->opt_kernels != 0;
     const bool tuned = tuned1 && h->canonical;         // two sweeps per pass: canonical stencil only
     if (L.vzero_next) {
         // CpuSolver.cpp:100-101 v.fill(0) followed by the pre-smoothing: the two-sweep kernel takes the zero iterate as a
@@ -531,7 +530,7 @@ int do_residual(gs_handle* h, int level, bool store_r, int zb, int ze)
     OpScope t(h, GS_OP_RESIDUAL, level);
     GS(need_v_halo(h, level, 1));
     bool handled = false;
-    if (h->opt_kernels && !h->cx.rec)
+    if (h->opt_kernels)
         CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), store_r ? L.r : nullptr, &handled,
                        gen_offsets(h)));
     if (!handled)
@@ -607,7 +606,7 @@ int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, dou
     int zb, ze;
     coarse_range(h, level, &zb, &ze);
     bool handled = false;
-    if (h->opt_kernels && !h->cx.rec) CU(kt_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2, &handled));
+    if (h->opt_kernels) CU(kt_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2, &handled));
     if (!handled) CU(ks_restrict(h->cx, F.g, C.g, zb, ze, fine, coarse, coarse2));
     GS(finish_coarse(h, level, coarse));
     if (coarse2) GS(finish_coarse(h, level, coarse2));
@@ -624,7 +623,7 @@ int do_restrict_residual(gs_handle* h, int level)
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     if (partitioned(h, level)) {
-        if (h->opt_kernels && h->canonical && !h->cx.rec) {
+        if (h->opt_kernels && h->canonical) {
             // overlapped: the coarse planes away from the slab boundaries first, a band of four at each side after the join
             constexpr int CB = 4;  // kt_resid_restrict takes no shorter range
             int czb, cze;
@@ -649,7 +648,7 @@ int do_restrict_residual(gs_handle* h, int level)
         GS(need_v_halo(h, level, 2));
         if (L.zlo > 0) zb = L.ib - 1;
     }
-    if (h->opt_kernels && h->canonical && !h->cx.rec) {
+    if (h->opt_kernels && h->canonical) {
         // fused: the residual never goes to memory (kernels_transfer.cu)
         int czb, cze;
         coarse_range(h, level, &czb, &cze);
@@ -660,7 +659,7 @@ int do_restrict_residual(gs_handle* h, int level)
     {
         // unfused: the residual goes to memory (config-driven offsets: GEN kernel; small levels: one thread per point)
         bool handled = false;
-        if (h->opt_kernels && !h->canonical && !h->cx.rec)
+        if (h->opt_kernels && !h->canonical)
             CU(kf_residual(h->cx, km, L.ar, L.g, zb, ze, L.k, L.v, L.f, smoother_aux(h, level, km), L.r, &handled, gen_offsets(h)));
         if (!handled) CU(ks_residual(h->cx, km, L.pow2, L.g, zb, ze, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r));
     }
@@ -704,7 +703,7 @@ int do_prolong_correct(gs_handle* h, int level)
     // field out of place in that case keeps the buffer parity (and the CUDA graph) fixed
     const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
     bool handled = false;
-    if (h->opt_kernels && !h->cx.rec) CU(kt_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, &handled));
+    if (h->opt_kernels) CU(kt_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, &handled));
     if (!handled) CU(ks_prolong_correct(h->cx, F.g, C.g, F.ib, F.ie, F.v, flip ? F.vtmp : F.v, C.v, nullptr));
     if (flip) std::swap(F.v, F.vtmp);
     F.gv = 0;
@@ -721,7 +720,7 @@ int try_prolong_smooth2(gs_handle* h, int level, bool* done)
     Level& C = h->lev[level + 1];
     const int km = smoother_km(h);
     const bool flip = ((h->p.pre + h->p.post) & 1) != 0;
-    if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || h->cx.rec || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
+    if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
         km == KM_NEWTON_EXP)
         return GS_OK;
     if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16) return GS_OK;  // kx_smooth2 would decline
@@ -753,46 +752,11 @@ int zero_field(gs_handle* h, Level& L, double* a)
     return GS_OK;
 }
 
-// first level of the coarse tail (run as one single-CTA kernel, kernels_simple.cu ks_tail_*), or -1.  Never the
-// coarsest level alone (nothing to merge), not on slabs, not while per-operator events are wanted.
-int plan_tail(const gs_params& p, i64 tail_points)
-{
-    if (tail_points <= 0) return -1;
-    const int last = num_levels_for(p) - 1;
-    for (int l = 0; l < last; l++) {
-        uint64_t n[3];
-        level_dims(p, l, n);
-        if ((i64)(n[0] * n[1] * n[2]) <= tail_points && last - l + 1 <= GS_TAIL_MAX_LEVELS) return l;
-    }
-    return -1;
-}
-
-int tail_first_level(const gs_handle* h)
-{
-    if (h->world != 1 || h->opt_timing) return -1;
-    return plan_tail(h->p, h->cx.tune.tail_points);
-}
-
-int tail_begin(gs_handle* h)
-{
-    if (!h->tail) h->tail = ks_tail_new();
-    ks_tail_begin(h->cx, h->tail);
-    return GS_OK;
-}
-
-int tail_end(gs_handle* h)
-{
-    cudaError_t e = ks_tail_end(h->cx);
-    if (e != cudaSuccess) return fail(GS_ECUDA, "coarse-tail kernel: %s", cudaGetErrorString(e));
-    return GS_OK;
-}
-
 // everything CpuSolver::vcycle (src/cpu/CpuSolver.cpp:85-139) does, queued on the stream
-int enqueue_vcycle_ops(gs_handle* h, int tail, bool host_norm)
+int enqueue_vcycle(gs_handle* h, bool host_norm = true)
 {
     const int last = (int)h->lev.size() - 1;
     for (int i = 0; i < last; i++) {
-        if (i == tail) GS(tail_begin(h));  // from here down to the coarsest level and back up to this level: recorded
         GS(do_smooth(h, i, h->p.pre));
         GS(do_restrict_residual(h, i));
         if (h->p.mode != GS_MODE_NONLINEAR) {
@@ -814,20 +778,10 @@ int enqueue_vcycle_ops(gs_handle* h, int tail, bool host_norm)
         GS(try_prolong_smooth2(h, i - 1, &fused));
         if (!fused) GS(do_prolong_correct(h, i - 1));
         GS(do_smooth(h, i - 1, h->p.post - (fused ? 2 : 0)));
-        if (i - 1 == tail) GS(tail_end(h));
     }
     GS(do_norm_residual(h));
     if (host_norm) GS(norm_to_host(h, 0));
     return GS_OK;
-}
-
-int enqueue_vcycle(gs_handle* h, bool host_norm = true)
-{
-    const int rc = enqueue_vcycle_ops(h, tail_first_level(h), host_norm);
-    if (h->cx.rec) {  // an operator failed while recording: drop the program, never leave the recorder attached
-        h->cx.rec = nullptr;
-    }
-    return rc;
 }
 
 // Key of a captured V-cycle: only the state that changes BETWEEN cycles of one handle — which of the two buffers is `v` on
@@ -1206,7 +1160,7 @@ int newton_compF(gs_handle* h, double* norm)
         // newtonF), expression for expression (gs_device.cuh finish_residual<KM_NONLINEAR> vs kernels_simple.cu
         // newton_F_simple): the tuned residual kernel computes it, stores it as f and reduces its norm
         bool handled = false;
-        if (h->opt_kernels && !h->cx.rec)
+        if (h->opt_kernels)
             CU(kf_residual(h->cx, KM_NONLINEAR, L.ar, L.g, L.ib, L.ie, L.k, L.newtonV, h->newtonF, nullptr, L.f, &handled, gen_offsets(h)));
         if (!handled) CU(ks_newton_F(h->cx, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.newtonV, h->newtonF, L.f));
         GS(exchange_halo(h, 0, L.f, 1));  // the residual+restriction of a slab reads f one plane outside it
@@ -1313,13 +1267,11 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->h_norm = nullptr;
     h->stage = nullptr;
     h->stage_count = 0;
-    h->tail = nullptr;
-    h->cx.rec = nullptr;
     h->arena = nullptr;
     h->arena_bytes = 0;
     h->opt_p2p = 1;
     if (const char* e = getenv("GPUSOLVE_P2P")) h->opt_p2p = atoi(e) != 0;
-    h->opt_fuse_pc = 0;
+    h->opt_fuse_pc = 1;  // validated on the GPU (profiles/r02a_*): same bits, one pass per level and cycle fewer
     if (const char* e = getenv("GPUSOLVE_FUSE_PC")) h->opt_fuse_pc = atoi(e) != 0;
     h->opt_device_stop = 1;
     if (const char* e = getenv("GPUSOLVE_DEVICE_STOP")) h->opt_device_stop = atoi(e) != 0;
@@ -1481,10 +1433,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->cx.tune.zchunk2 = 128;
     h->cx.tune.wave = 1;
     if (const char* ev = getenv("GPUSOLVE_WAVE")) h->cx.tune.wave = atoi(ev) != 0;
-    if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(2, atoi(ev)));
-    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = std::max(0, std::min(2, atoi(ev)));
-    h->cx.tune.tail_points = 0;  // coarse tail as one single-CTA kernel: prepared, off until it has been through the GPU suite
-    if (const char* ev = getenv("GPUSOLVE_TAIL_POINTS")) h->cx.tune.tail_points = std::max(0, std::min(1 << 20, atoi(ev)));
+    if (const char* ev = getenv("GPUSOLVE_FUSE2")) h->cx.tune.fuse2 = std::max(0, std::min(1, atoi(ev)));
+    if (const char* ev = getenv("GPUSOLVE_RR_VARIANT")) h->cx.tune.rr_variant = std::max(0, std::min(1, atoi(ev)));
     e = kf_prepare();
     if (e == cudaSuccess) e = kt_prepare();
     if (e == cudaSuccess) e = kx_prepare();
@@ -1617,7 +1567,6 @@ int gs_destroy(gs_handle* h)
     }
     for (auto e : h->ev_free) cudaEventDestroy(e);
     if (h->comm) gs_comm_destroy(h->comm);
-    if (h->tail) ks_tail_free(h->tail);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->stream2) cudaStreamDestroy(h->stream2);
@@ -1649,13 +1598,6 @@ int gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int ove
     LaunchCtx cx{};
     cx.sm_count = sm_count;
     return gs_pick_zchunk_waves(cx, tiles, planes, ctas_per_sm, overhead, min_chunk, max_chunk, even != 0);
-}
-
-int gs_plan_tail(const gs_params* p, int64_t tail_points)
-{
-    if (!p) return fail(GS_EINVAL, "null argument");
-    GS(validate(*p));
-    return plan_tail(*p, tail_points);
 }
 
 int gs_num_levels(const gs_handle* h) { return h ? (int)h->lev.size() : fail(GS_EINVAL, "null handle"); }
@@ -2012,11 +1954,10 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "device_stop") h->opt_device_stop = value != 0;
     else if (n == "p2p") h->opt_p2p = value != 0;
     else if (n == "fuse_pc") h->opt_fuse_pc = value != 0;
-    else if (n == "tail_points") h->cx.tune.tail_points = (int)std::max<int64_t>(0, std::min<int64_t>(1 << 20, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;
         for (auto& L : h->lev) L.ar = level_ar(L, h->opt_unit != 0, h->opt_rcp_div != 0);
-    } else if (n == "rr_variant") h->cx.tune.rr_variant = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
+    } else if (n == "rr_variant") h->cx.tune.rr_variant = (int)std::max<int64_t>(0, std::min<int64_t>(1, value));
     else if (n == "fuse2") {
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
         h->lev[0].pre_valid = 0;

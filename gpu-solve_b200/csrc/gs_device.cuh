@@ -96,8 +96,8 @@ enum { AR_POW2 = 1, AR_UNIT = 2, AR_RCP = 4 };
         }                                                                       \
     } while (0)
 
-// The point functions are __host__ __device__ only so that a CPU test can run the coarse-tail interpreter of
-// kernels_simple.cu over host arrays (tests/tail_host_check.cu); the library itself never calls them on the host.
+// The point functions are __host__ __device__ only so that a CPU test can run them over host arrays
+// (tests/pc_host_check.cu); the library itself never calls them on the host.
 #define GS_HD __host__ __device__ __forceinline__
 #ifdef __CUDA_ARCH__
 #define GS_FMA(a, b, c) __fma_rn(a, b, c)

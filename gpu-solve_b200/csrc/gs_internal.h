@@ -64,16 +64,12 @@ struct Tune {
     int smooth_variant;  // 0 simple, 1x z-march through L1, 2x TMA-staged z-march (kernels_fast.cu)
     int zchunk;          // planes per CTA of the z-marching kernels
     int fast_min_n;      // levels with fewer interior points per axis use the simple kernels
-    int rr_variant;      // fused residual+restriction kernel: 0 = five-stage ring, 1 = six-stage (default), 2 = split-phase barrier (prepared, unvalidated)
+    int rr_variant;      // fused residual+restriction kernel: 0 = five-stage ring, 1 = six-stage (default)
     int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1 = five-stage ring, 2 = four-stage
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
     int zchunk2;         // planes per CTA of the two-sweep kernel
     int wave;            // 1: size z chunks so the grid fills whole waves of resident CTAs (gs_pick_zchunk_waves)
-    int tail_points;     // > 0: levels with at most this many interior points run as ONE single-CTA kernel per V-cycle (ks_tail_*); 0 = off
 };
-
-struct TailRec;  // kernels_simple.cu: the operator list of the coarse tail of a V-cycle
-constexpr int GS_TAIL_MAX_LEVELS = 6;  // levels one tail program can address (its level table travels in the kernel parameters)
 
 struct LaunchCtx {
     cudaStream_t stream;
@@ -81,7 +77,6 @@ struct LaunchCtx {
     NormBuf norm;
     uint64_t* launches;   // host counter of kernels launched
     int sm_count;
-    TailRec* rec;         // non-null while the coarse tail is being recorded: ks_* append to it instead of launching
 };
 
 // ---- kernels_ctl.cu: device-side stopping test of the solve loop (conditional CUDA graph) ----
@@ -123,17 +118,9 @@ cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* 
 // analytic right-hand side, src/cpu/CpuGridData.cpp:45-78 (local planes [0, nzl))
 cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f);
 
-// whole-array helpers that take part in the recording (plain cudaMemsetAsync / cudaMemcpyAsync otherwise)
+// whole-array helpers (cudaMemsetAsync / cudaMemcpyAsync on the stream)
 cudaError_t ks_zero(const LaunchCtx& cx, double* a, size_t count);
 cudaError_t ks_copy(const LaunchCtx& cx, double* dst, const double* src, size_t count);
-// Coarse tail: the levels below ~16^3 cost a few microseconds of launch latency per operator and nothing else.  Between
-// ks_tail_begin and ks_tail_end every ks_* call above is appended to a program instead of being launched, and ks_tail_end
-// runs the program as one kernel of one CTA (operators separated by __syncthreads, same per-point functions, hence
-// the same bits).  The program travels as a kernel parameter, so a captured graph needs no device-side copy of it.
-TailRec* ks_tail_new();
-void ks_tail_free(TailRec* r);
-void ks_tail_begin(LaunchCtx& cx, TailRec* r);
-cudaError_t ks_tail_end(LaunchCtx& cx);
 
 // ---- kernels_fast.cu: tuned sm_100a kernels for the canonical axis-aligned stencil ----
 bool kf_available();

@@ -37,8 +37,8 @@ GS_HD double tap_sum(const double* __restrict__ a, i64 c, const double (&cv)[7],
     return s;
 }
 
-// The per-point bodies are functions of (x, y, local plane) so that the grid kernels below and the single-CTA tail
-// kernel at the end of this file run the very same code.
+// The per-point bodies are functions of (x, y, local plane), shared by the grid kernels below (and by the CPU check of the
+// interpolation state machine, tests/pc_host_check.cu).
 template <int KM, bool POW2>
 GS_HD void smooth_point(const Geom& g, const PointK& k, const i64 (&toff)[7], const double* vin, double* vout,
                                              const double* f, const double* auxp, int x, int y, int zl)
@@ -330,117 +330,6 @@ __global__ void __launch_bounds__(BX* BY) init_rhs_simple(Geom g, int mode, doub
 }
 
 
-// ---------------------------------------------------------------------------------
-// coarse tail: a recorded list of the operators above, run by ONE CTA (gs_internal.h ks_tail_*)
-// ---------------------------------------------------------------------------------
-enum { T_SMOOTH, T_RESID, T_RESTRICT, T_PROLONG, T_FAS, T_COEF, T_AXPY, T_ZERO, T_COPY };
-constexpr int TAIL_THREADS = 1024, TAIL_MAX_OPS = 44, TAIL_MAX_LEV = GS_TAIL_MAX_LEVELS;
-
-struct TailLev {
-    Geom g;
-    PointK k;
-    i64 toff[7];
-};
-
-struct TailOp {
-    unsigned char type, pow2;
-    unsigned char la, lb;  // level-table entries: the level (fine level of a transfer), the coarse level of a transfer
-    int sign;
-    int zb, nz;            // first local plane and number of planes of the points to visit
-    const double *a, *b, *c;  // inputs, in the order of the ks_* signature
-    double *o, *o2;           // outputs
-    union {
-        double gamma;  // T_COEF
-        i64 count;     // T_ZERO / T_COPY: doubles
-    };
-};
-
-struct TailProg {
-    int nops, nlev;
-    TailLev lev[TAIL_MAX_LEV];
-    TailOp op[TAIL_MAX_OPS];
-};
-// the program is passed as a kernel parameter and stays inside the classic 4 KB parameter space (no reliance on the
-// 32 KB limit of newer drivers): a V(3,3) tail of four levels is 37 operators; longer ones are split by the recorder
-static_assert(sizeof(TailOp) == 64 && sizeof(TailProg) <= 4096, "tail program must fit the 4 KB kernel parameter space");
-
-// visit the nx*ny*nz points of planes [zb, zb+nz), x fastest, nthr at a time
-template <typename F>
-GS_HD void tail_points(int nx, int ny, int nz, int zb, int tid, int nthr, F body)
-{
-    const int n = nx * ny * nz;
-    for (int i = tid; i < n; i += nthr) {
-        const int x = i % nx, t = i / nx;
-        body(x + 1, t % ny + 1, t / ny + zb);
-    }
-}
-
-// thread `tid` of `nthr`: its share of one recorded operator.  KM is the same for every smoother / residual operator of
-// a cycle.  Loads are plain ld.global (no __ldg): the arrays are rewritten inside the kernel, by the same CTA.
-template <int KM>
-GS_HD void tail_do_op(const TailProg& P, const TailOp& op, int tid, int nthr)
-{
-    const TailLev& A = P.lev[op.la];
-    const TailLev& B = P.lev[op.lb];
-    switch (op.type) {
-    case T_SMOOTH:
-        if (op.pow2)
-            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                        [&](int x, int y, int z) { smooth_point<KM, true>(A.g, A.k, A.toff, op.a, op.o, op.b, op.c, x, y, z); });
-        else
-            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                        [&](int x, int y, int z) { smooth_point<KM, false>(A.g, A.k, A.toff, op.a, op.o, op.b, op.c, x, y, z); });
-        break;
-    case T_RESID:
-        if (op.pow2)
-            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                        [&](int x, int y, int z) { residual_point<KM, true>(A.g, A.k, A.toff, op.a, op.b, op.c, op.o, x, y, z); });
-        else
-            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                        [&](int x, int y, int z) { residual_point<KM, false>(A.g, A.k, A.toff, op.a, op.b, op.c, op.o, x, y, z); });
-        break;
-    case T_RESTRICT:
-        tail_points(B.g.nx, B.g.ny, op.nz, op.zb, tid, nthr,
-                    [&](int x, int y, int z) { restrict_point(A.g, B.g, op.a, op.o, op.o2, x, y, z); });
-        break;
-    case T_PROLONG:
-        tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                    [&](int x, int y, int z) { prolong_correct_point(A.g, B.g, op.a, op.o, op.b, op.o2, x, y, z); });
-        break;
-    case T_FAS:
-        if (op.pow2)
-            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                        [&](int x, int y, int z) { fas_rhs_point<true>(A.g, A.k, A.toff, op.a, op.o, op.o2, x, y, z); });
-        else
-            tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                        [&](int x, int y, int z) { fas_rhs_point<false>(A.g, A.k, A.toff, op.a, op.o, op.o2, x, y, z); });
-        break;
-    case T_COEF:
-        tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr,
-                    [&](int x, int y, int z) { newton_coef_point(A.g, op.gamma, op.a, op.o, x, y, z); });
-        break;
-    case T_AXPY:
-        tail_points(A.g.nx, A.g.ny, op.nz, op.zb, tid, nthr, [&](int x, int y, int z) { axpy_point(A.g, op.o, op.a, op.sign, x, y, z); });
-        break;
-    case T_ZERO:
-        for (i64 j = tid; j < op.count; j += nthr) op.o[j] = 0.0;
-        break;
-    case T_COPY:
-        for (i64 j = tid; j < op.count; j += nthr) op.o[j] = op.a[j];
-        break;
-    }
-}
-
-// one CTA runs the whole program; __syncthreads orders one operator after the other
-template <int KM>
-__global__ void __launch_bounds__(TAIL_THREADS, 1) tail_kernel(const __grid_constant__ TailProg P)
-{
-    for (int i = 0; i < P.nops; i++) {
-        tail_do_op<KM>(P, P.op[i], threadIdx.x, TAIL_THREADS);
-        __syncthreads();
-    }
-}
-
 inline dim3 grid_for(int nx, int ny, int nz) { return dim3((nx + BX - 1) / BX, (ny + BY - 1) / BY, nz); }
 
 inline void fill_toff(const Geom& g, const StencilOff& so, i64 (&toff)[7])
@@ -456,134 +345,14 @@ inline cudaError_t done(const LaunchCtx& cx)
 
 }  // namespace
 
-// ---- coarse-tail recorder -----------------------------------------------------------
-struct TailRec {
-    TailProg prog;
-    int km;
-    bool overflow;  // more distinct levels than the table holds (cannot happen: one entry per level, 12 levels at most)
-    bool has_k[TAIL_MAX_LEV];  // entry carries the point constants (made or completed by a smoother-type operator)
-    // how a finished program is executed: the CUDA launch below.  tests/tail_host_check.cu substitutes an interpreter
-    // over host arrays to check the recorder and tail_do_op without a GPU.
-    cudaError_t (*exec)(const LaunchCtx& cx, const TailProg& P, int km);
-};
-
-namespace {
-
-int tail_level(TailRec* r, const Geom& g, const PointK* k, const StencilOff* so)
-{
-    TailLev e;
-    memset(&e, 0, sizeof e);
-    e.g = g;
-    if (k) e.k = *k;
-    if (so) fill_toff(g, *so, e.toff);
-    TailProg& P = r->prog;
-    for (int i = 0; i < P.nlev; i++) {
-        if (memcmp(&P.lev[i].g, &g, sizeof g) != 0) continue;
-        if (!k) return i;  // a transfer operator only needs the geometry
-        if (!r->has_k[i]) {  // entry made by a transfer operator: complete it (nothing recorded so far reads its constants)
-            P.lev[i] = e;
-            r->has_k[i] = true;
-            return i;
-        }
-        if (memcmp(&P.lev[i].k, &e.k, sizeof e.k) == 0 && memcmp(P.lev[i].toff, e.toff, sizeof e.toff) == 0) return i;
-    }
-    if (P.nlev == TAIL_MAX_LEV) {
-        r->overflow = true;
-        return 0;
-    }
-    P.lev[P.nlev] = e;
-    r->has_k[P.nlev] = k != nullptr;
-    return P.nlev++;
-}
-
-cudaError_t tail_exec_cuda(const LaunchCtx& cx, const TailProg& P, int km)
-{
-    switch (km) {
-    case KM_LINEAR: tail_kernel<KM_LINEAR><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
-    case KM_NONLINEAR: tail_kernel<KM_NONLINEAR><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
-    case KM_NEWTON_EXP: tail_kernel<KM_NEWTON_EXP><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
-    default: tail_kernel<KM_NEWTON_COEF><<<1, TAIL_THREADS, 0, cx.stream>>>(P); break;
-    }
-    return done(cx);
-}
-
-cudaError_t tail_launch(const LaunchCtx& cx, TailRec* r)
-{
-    TailProg& P = r->prog;
-    if (P.nops == 0) return cudaSuccess;
-    if (r->overflow) return cudaErrorInvalidValue;
-    cudaError_t e = r->exec(cx, P, r->km);
-    P.nops = 0;  // the level table stays: the next program of the same tail uses the same levels
-    return e;
-}
-
-// append an operator; a full program is launched and a new one started (same semantics, one more kernel)
-cudaError_t tail_push(const LaunchCtx& cx, const TailOp& op)
-{
-    TailRec* r = cx.rec;
-    if (r->prog.nops == TAIL_MAX_OPS) {
-        cudaError_t e = tail_launch(cx, r);
-        if (e != cudaSuccess) return e;
-    }
-    r->prog.op[r->prog.nops++] = op;
-    return r->overflow ? cudaErrorInvalidValue : cudaSuccess;
-}
-
-TailOp tail_op(int type)
-{
-    TailOp op;
-    memset(&op, 0, sizeof op);
-    op.type = type;
-    return op;
-}
-
-}  // namespace
-
-TailRec* ks_tail_new()
-{
-    TailRec* r = new TailRec;
-    memset(&r->prog, 0, sizeof r->prog);
-    r->km = KM_LINEAR;
-    r->overflow = false;
-    r->exec = tail_exec_cuda;
-    return r;
-}
-
-void ks_tail_free(TailRec* r) { delete r; }
-
-void ks_tail_begin(LaunchCtx& cx, TailRec* r)
-{
-    r->prog.nops = 0;
-    r->prog.nlev = 0;
-    r->km = KM_LINEAR;
-    r->overflow = false;
-    cx.rec = r;
-}
-
-cudaError_t ks_tail_end(LaunchCtx& cx)
-{
-    TailRec* r = cx.rec;
-    cx.rec = nullptr;
-    return r ? tail_launch(cx, r) : cudaSuccess;
-}
-
 cudaError_t ks_zero(const LaunchCtx& cx, double* a, size_t count)
 {
-    if (!cx.rec) return cudaMemsetAsync(a, 0, count * sizeof(double), cx.stream);
-    TailOp op = tail_op(T_ZERO);
-    op.o = a;
-    op.count = (i64)count;
-    return tail_push(cx, op);
+    return cudaMemsetAsync(a, 0, count * sizeof(double), cx.stream);
 }
 
 cudaError_t ks_copy(const LaunchCtx& cx, double* dst, const double* src, size_t count)
 {
-    if (!cx.rec) return cudaMemcpyAsync(dst, src, count * sizeof(double), cudaMemcpyDeviceToDevice, cx.stream);
-    TailOp op = tail_op(T_COPY);
-    op.o = dst;
-    op.a = src;
-    op.count = (i64)count;
-    return tail_push(cx, op);
+    return cudaMemcpyAsync(dst, src, count * sizeof(double), cudaMemcpyDeviceToDevice, cx.stream);
 }
 
 #define KM_DISPATCH(KERNEL, km, pow2, ...)                                                          \
@@ -609,19 +378,6 @@ cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int
                       const StencilOff& so, const double* vin, double* vout, const double* f, const double* aux)
 {
     if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaSuccess;
-    if (cx.rec) {
-        TailOp op = tail_op(T_SMOOTH);
-        cx.rec->km = km;
-        op.pow2 = pow2;
-        op.la = tail_level(cx.rec, g, &k, &so);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = vin;
-        op.b = f;
-        op.c = aux;
-        op.o = vout;
-        return tail_push(cx, op);
-    }
     SmoothP p{g, k, {}, zb, vin, vout, f, aux};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -633,19 +389,6 @@ cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
                         const StencilOff& so, const double* v, const double* f, const double* aux, double* r)
 {
     if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaErrorInvalidValue;
-    if (cx.rec) {  // inside the tail only the stored residual matters (its norm is never read)
-        TailOp op = tail_op(T_RESID);
-        cx.rec->km = km;
-        op.pow2 = pow2;
-        op.la = tail_level(cx.rec, g, &k, &so);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = v;
-        op.b = f;
-        op.c = aux;
-        op.o = r;
-        return tail_push(cx, op);
-    }
     ResidP p{g, k, {}, zb, v, f, aux, r, cx.norm};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -658,17 +401,6 @@ cudaError_t ks_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int
                         double* coarse, double* coarse2)
 {
     if (ze <= zb || gc.nx <= 0 || gc.ny <= 0) return cudaSuccess;
-    if (cx.rec) {
-        TailOp op = tail_op(T_RESTRICT);
-        op.la = tail_level(cx.rec, gf, nullptr, nullptr);
-        op.lb = tail_level(cx.rec, gc, nullptr, nullptr);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = fine;
-        op.o = coarse;
-        op.o2 = coarse2;
-        return tail_push(cx, op);
-    }
     RestrictP p{gf, gc, zb, fine, coarse, coarse2};
     restrict_simple<<<grid_for(gc.nx, gc.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
     return done(cx);
@@ -678,19 +410,6 @@ cudaError_t ks_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
                                double* vout, const double* coarse, double* e_out)
 {
     if (ze <= zb) return cudaSuccess;
-    if (cx.rec) {
-        if (gf.nx <= 0 || gf.ny <= 0) return cudaSuccess;
-        TailOp op = tail_op(T_PROLONG);
-        op.la = tail_level(cx.rec, gf, nullptr, nullptr);
-        op.lb = tail_level(cx.rec, gc, nullptr, nullptr);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = vin;
-        op.b = coarse;
-        op.o = vout;
-        op.o2 = e_out;
-        return tail_push(cx, op);
-    }
     ProlongP p{gf, gc, zb, vin, vout, coarse, e_out};
     prolong_correct_simple<<<grid_for(gf.nx, gf.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
     return done(cx);
@@ -700,17 +419,6 @@ cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, in
                        const StencilOff& so, const double* restv, double* f, double* r_out)
 {
     if (ze <= zb) return cudaSuccess;
-    if (cx.rec) {
-        TailOp op = tail_op(T_FAS);
-        op.pow2 = pow2;
-        op.la = tail_level(cx.rec, g, &k, &so);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = restv;
-        op.o = f;
-        op.o2 = r_out;
-        return tail_push(cx, op);
-    }
     FasP p{g, k, {}, zb, restv, f, r_out};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -722,7 +430,7 @@ cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, in
 cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
                         const StencilOff& so, const double* nv, const double* newtonF, double* f)
 {
-    if (ze <= zb || cx.rec) return cudaErrorInvalidValue;  // level 0 with its norm: never part of a tail
+    if (ze <= zb) return cudaErrorInvalidValue;
     NewtonFP p{g, k, {}, zb, nv, newtonF, f, cx.norm};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
@@ -735,16 +443,6 @@ cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, i
 cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, double gamma, const double* nv, double* coef)
 {
     if (ze <= zb) return cudaSuccess;
-    if (cx.rec) {
-        TailOp op = tail_op(T_COEF);
-        op.la = tail_level(cx.rec, g, nullptr, nullptr);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = nv;
-        op.o = coef;
-        op.gamma = gamma;
-        return tail_push(cx, op);
-    }
     newton_coef_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, gamma, nv, coef);
     return done(cx);
 }
@@ -752,23 +450,12 @@ cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, d
 cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* dst, const double* src, int sign)
 {
     if (ze <= zb) return cudaSuccess;
-    if (cx.rec) {
-        TailOp op = tail_op(T_AXPY);
-        op.la = tail_level(cx.rec, g, nullptr, nullptr);
-        op.zb = zb;
-        op.nz = ze - zb;
-        op.a = src;
-        op.o = dst;
-        op.sign = sign;
-        return tail_push(cx, op);
-    }
     axpy_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, dst, src, sign);
     return done(cx);
 }
 
 cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f)
 {
-    if (cx.rec) return cudaErrorInvalidValue;
     init_rhs_simple<<<grid_for(g.X, g.Y, g.nzl), dim3(BX, BY), 0, cx.stream>>>(g, mode, h, gamma, f);
     return done(cx);
 }

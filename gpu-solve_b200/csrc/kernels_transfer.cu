@@ -224,12 +224,7 @@ struct ResidRestrictP {
 // tells that every warp is done with the planes before it (no empty barriers).  An earlier version with a producer warp
 // and full/empty mbarriers lost parity when launched back to back (a stage was refilled while slow warps still read it;
 // tools/debug_ops.py reproduces such races), and was slower.
-// SP (prepared, not the default until it has been through the GPU race test): split-phase barrier.  A warp ARRIVES on an
-// mbarrier after storing residual plane 2j+2 and WAITS only after it has also computed plane 2j+3, so slow warps have a
-// fine plane of slack instead of stalling everybody at a CTA barrier per coarse plane (22 % of the stalls, ncu).  Needs
-// a sixth residual slot (plane 2j+3 is written while plane 2j-2 may still be read) and reads its own residuals of
-// planes 2j+1, 2j+2 back from shared memory.
-template <int CX, int CY, int NSTAGE, bool SP = false>
+template <int CX, int CY, int NSTAGE>
 struct RRCfg {
     // the first coarse plane reads v planes 0..4 before the first CTA barrier, so the ring must hold five
     static_assert(NSTAGE >= 5, "resid_restrict_tma needs at least five stages");
@@ -240,27 +235,26 @@ struct RRCfg {
     static constexpr int RH = FY + 1;               // residual rows y = 2*Y0-1 .. 2*(Y0+CY)-1
     static constexpr int ROW_O = CX + 1, ROW_E = CX;
     static constexpr int RSLOT = RH * (ROW_O + ROW_E);  // doubles per residual plane
-    static constexpr int NSLOT = SP ? 6 : 5;
+    static constexpr int NSLOT = 5;
     static constexpr int NCOMP = CX * CY;
     static constexpr int NSTRIP_USED = RH + FX;
     static constexpr int NSTRIP = (NSTRIP_USED + 31) / 32 * 32;
     static constexpr int NCONS = NCOMP + NSTRIP;
     static constexpr int THREADS = NCONS;
-    static constexpr int SMEM = NSTAGE * V_STRIDE + NSLOT * RSLOT * 8 + (NSTAGE + (SP ? 1 : 0)) * 8 + 128;
+    static constexpr int SMEM = NSTAGE * V_STRIDE + NSLOT * RSLOT * 8 + NSTAGE * 8 + 128;
 };
 
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
-template <int KM, int AR, int CX, int CY, int NSTAGE, bool SP>
-__global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE, SP>::THREADS, 2)
+template <int KM, int AR, int CX, int CY, int NSTAGE>
+__global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
     resid_restrict_tma(const __grid_constant__ CUtensorMap map_v, ResidRestrictP p)
 {
-    using Cfg = RRCfg<CX, CY, NSTAGE, SP>;
+    using Cfg = RRCfg<CX, CY, NSTAGE>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned char* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
     double* rbuf = (double*)(smem + NSTAGE * Cfg::V_STRIDE);
     uint64_t* full = (uint64_t*)(rbuf + Cfg::NSLOT * Cfg::RSLOT);
-    uint64_t* rbar = full + NSTAGE;  // SP only: phase j completes when every warp has stored residual plane 2j+2
 
     const int tid = threadIdx.x;
     const int X0 = 1 + blockIdx.x * CX, Y0 = 1 + blockIdx.y * CY;
@@ -280,7 +274,6 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE, SP>::THREADS, 2)
     int next = 0;  // thread 0: first plane not yet requested
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; s++) mbar_init(&full[s], 1);
-        if (SP) mbar_init(rbar, Cfg::NCONS / 32);
         mbar_fence_init();
         for (; next < NSTAGE && next < nvp; next++) issue(next);
     }
@@ -380,70 +373,31 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE, SP>::THREADS, 2)
         do_plane(0);
         const bool live = X <= p.gc.nx && Y <= p.gc.ny;
         i64 cc = gs_idx(p.gc, min(X, p.gc.nx), min(Y, p.gc.ny), zc0);
-        if (!SP) {
-            for (int j = 0; j < nzc; j++) {
-                do_plane(2 * j + 1);
-                rB11 = r11; rB21 = r21; rB12 = r12; rB22 = r22;
-                do_plane(2 * j + 2);
-                consumer_sync<Cfg::NCONS>();
-                refill(j);
-                const double* sA = slot(2 * j);
-                const double* sB = slot(2 * j + 1);
-                const double* sC = slot(2 * j + 2);
-                const int oO = (2 * ly) * Cfg::ROW_O + lx, oE = EOFF + (2 * ly) * Cfg::ROW_E + lx;
-                double acc = 0.0;
-                // ii = -1: x1 = 2X-1 (odd block)
-                TERM(0.5, 0.5, sA[oO], rB11, r11)
-                TERM(0.5, 1.0, sA[oO + Cfg::ROW_O], rB12, r12)
-                TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O], sB[oO + 2 * Cfg::ROW_O], sC[oO + 2 * Cfg::ROW_O])
-                // ii = 0: x2 = 2X (even block)
-                TERM(1.0, 0.5, sA[oE], rB21, r21)
-                TERM(1.0, 1.0, sA[oE + Cfg::ROW_E], rB22, r22)
-                TERM(1.0, 0.5, sA[oE + 2 * Cfg::ROW_E], sB[oE + 2 * Cfg::ROW_E], sC[oE + 2 * Cfg::ROW_E])
-                // ii = +1: x3 = 2X+1 (odd block, next column)
-                TERM(0.5, 0.5, sA[oO + 1], sB[oO + 1], sC[oO + 1])
-                TERM(0.5, 1.0, sA[oO + Cfg::ROW_O + 1], sB[oO + Cfg::ROW_O + 1], sC[oO + Cfg::ROW_O + 1])
-                TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O + 1], sB[oO + 2 * Cfg::ROW_O + 1], sC[oO + 2 * Cfg::ROW_O + 1])
-                if (live) p.coarse[cc] = acc;
-                cc += p.gc.plane;
-            }
-        } else {
-            // split phase: plane 2j+3 is computed before the wait for phase j (not in the first iteration: its v planes are
-            // requested by the refill that follows the wait); the thread's own residuals of planes 2j+1 and 2j+2 come back
-            // from the slots, because the registers already hold plane 2j+3
-            const bool lane0 = (tid & 31) == 0;
+        for (int j = 0; j < nzc; j++) {
+            do_plane(2 * j + 1);
+            rB11 = r11; rB21 = r21; rB12 = r12; rB22 = r22;
+            do_plane(2 * j + 2);
+            consumer_sync<Cfg::NCONS>();
+            refill(j);
+            const double* sA = slot(2 * j);
+            const double* sB = slot(2 * j + 1);
+            const double* sC = slot(2 * j + 2);
             const int oO = (2 * ly) * Cfg::ROW_O + lx, oE = EOFF + (2 * ly) * Cfg::ROW_E + lx;
-            do_plane(1);
-            do_plane(2);
-            __syncwarp();
-            if (lane0) mbar_arrive(rbar);
-            for (int j = 0; j < nzc; j++) {
-                const bool more = j + 1 < nzc;
-                if (more && j > 0) do_plane(2 * j + 3);
-                mbar_wait(rbar, j & 1);
-                refill(j);
-                const double* sA = slot(2 * j);
-                const double* sB = slot(2 * j + 1);
-                const double* sC = slot(2 * j + 2);
-                double acc = 0.0;
-                TERM(0.5, 0.5, sA[oO], sB[oO], sC[oO])
-                TERM(0.5, 1.0, sA[oO + Cfg::ROW_O], sB[oO + Cfg::ROW_O], sC[oO + Cfg::ROW_O])
-                TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O], sB[oO + 2 * Cfg::ROW_O], sC[oO + 2 * Cfg::ROW_O])
-                TERM(1.0, 0.5, sA[oE], sB[oE], sC[oE])
-                TERM(1.0, 1.0, sA[oE + Cfg::ROW_E], sB[oE + Cfg::ROW_E], sC[oE + Cfg::ROW_E])
-                TERM(1.0, 0.5, sA[oE + 2 * Cfg::ROW_E], sB[oE + 2 * Cfg::ROW_E], sC[oE + 2 * Cfg::ROW_E])
-                TERM(0.5, 0.5, sA[oO + 1], sB[oO + 1], sC[oO + 1])
-                TERM(0.5, 1.0, sA[oO + Cfg::ROW_O + 1], sB[oO + Cfg::ROW_O + 1], sC[oO + Cfg::ROW_O + 1])
-                TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O + 1], sB[oO + 2 * Cfg::ROW_O + 1], sC[oO + 2 * Cfg::ROW_O + 1])
-                if (live) p.coarse[cc] = acc;
-                cc += p.gc.plane;
-                if (more) {
-                    if (j == 0) do_plane(3);
-                    do_plane(2 * j + 4);
-                    __syncwarp();
-                    if (lane0) mbar_arrive(rbar);
-                }
-            }
+            double acc = 0.0;
+            // ii = -1: x1 = 2X-1 (odd block)
+            TERM(0.5, 0.5, sA[oO], rB11, r11)
+            TERM(0.5, 1.0, sA[oO + Cfg::ROW_O], rB12, r12)
+            TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O], sB[oO + 2 * Cfg::ROW_O], sC[oO + 2 * Cfg::ROW_O])
+            // ii = 0: x2 = 2X (even block)
+            TERM(1.0, 0.5, sA[oE], rB21, r21)
+            TERM(1.0, 1.0, sA[oE + Cfg::ROW_E], rB22, r22)
+            TERM(1.0, 0.5, sA[oE + 2 * Cfg::ROW_E], sB[oE + 2 * Cfg::ROW_E], sC[oE + 2 * Cfg::ROW_E])
+            // ii = +1: x3 = 2X+1 (odd block, next column)
+            TERM(0.5, 0.5, sA[oO + 1], sB[oO + 1], sC[oO + 1])
+            TERM(0.5, 1.0, sA[oO + Cfg::ROW_O + 1], sB[oO + Cfg::ROW_O + 1], sC[oO + Cfg::ROW_O + 1])
+            TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O + 1], sB[oO + 2 * Cfg::ROW_O + 1], sC[oO + 2 * Cfg::ROW_O + 1])
+            if (live) p.coarse[cc] = acc;
+            cc += p.gc.plane;
         }
 #undef TERM
     } else {
@@ -489,29 +443,10 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE, SP>::THREADS, 2)
             D = C; C = U; fv = nf; av = na;
         };
         do_plane(0);
-        if (!SP) {
-            for (int j = 0; j < nzc; j++) {
-                do_plane(2 * j + 1);
-                do_plane(2 * j + 2);
-                consumer_sync<Cfg::NCONS>();
-            }
-        } else {
-            const bool lane0 = (tid & 31) == 0;
-            do_plane(1);
-            do_plane(2);
-            __syncwarp();
-            if (lane0) mbar_arrive(rbar);
-            for (int j = 0; j < nzc; j++) {
-                const bool more = j + 1 < nzc;
-                if (more && j > 0) do_plane(2 * j + 3);
-                mbar_wait(rbar, j & 1);
-                if (more) {
-                    if (j == 0) do_plane(3);
-                    do_plane(2 * j + 4);
-                    __syncwarp();
-                    if (lane0) mbar_arrive(rbar);
-                }
-            }
+        for (int j = 0; j < nzc; j++) {
+            do_plane(2 * j + 1);
+            do_plane(2 * j + 2);
+            consumer_sync<Cfg::NCONS>();
         }
     }
 }
@@ -565,17 +500,17 @@ cudaError_t kt_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int
 
 namespace {
 
-template <int KM, int AR, int CX, int CY, int NSTAGE, bool SP>
+template <int KM, int AR, int CX, int CY, int NSTAGE>
 cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 {
-    using Cfg = RRCfg<CX, CY, NSTAGE, SP>;
+    using Cfg = RRCfg<CX, CY, NSTAGE>;
     static DevOnce once;
     int occ = 1;
     cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
-        cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, AR, CX, CY, NSTAGE, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, AR, CX, CY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, resid_restrict_tma<KM, AR, CX, CY, NSTAGE, SP>, Cfg::THREADS, Cfg::SMEM);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, resid_restrict_tma<KM, AR, CX, CY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
         return e;
     });
     if (pe != cudaSuccess) return pe;
@@ -587,7 +522,7 @@ cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
     if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tx * ty, p.zce - p.zcb, occ, 3, 4, 64, false);
     else p.zchunk = gs_pick_zchunk(cx, tx * ty, p.zce - p.zcb, 32);
     dim3 grid(tx, ty, (p.zce - p.zcb + p.zchunk - 1) / p.zchunk);
-    resid_restrict_tma<KM, AR, CX, CY, NSTAGE, SP><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, p);
+    resid_restrict_tma<KM, AR, CX, CY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, p);
     *handled = true;
     return cudaGetLastError();
 }
@@ -595,9 +530,8 @@ cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 template <int KM, int AR>
 cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, bool* handled)
 {
-    if (cfg == 1) return launch_rr<KM, AR, 32, 8, 6, false>(cx, p, handled);
-    if (cfg == 2) return launch_rr<KM, AR, 32, 8, 5, true>(cx, p, handled);  // prepared: split-phase barrier, not validated yet
-    return launch_rr<KM, AR, 32, 8, 5, false>(cx, p, handled);
+    if (cfg == 1) return launch_rr<KM, AR, 32, 8, 6>(cx, p, handled);
+    return launch_rr<KM, AR, 32, 8, 5>(cx, p, handled);
 }
 
 }  // namespace
@@ -616,7 +550,7 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& g
     }
     ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse};
     cudaError_t e = cudaSuccess;
-    for (int c = v ? cfg : 0; c <= (v ? cfg : 2) && e == cudaSuccess; c++) {
+    for (int c = v ? cfg : 0; c <= (v ? cfg : 1) && e == cudaSuccess; c++) {
 #define CALL(KMV) AR_SWITCH(ar, e = (dispatch_rr<KMV, ARV>(cx, p, c, handled)))
         switch (km) {
         case KM_LINEAR: CALL(KM_LINEAR); break;

@@ -19,18 +19,13 @@ extern "C" {
 int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int overhead,
                     int min_chunk, int max_chunk, int even);
 
-/* first level of the coarse tail for option "tail_points" = tail_points (levels of at most that many interior points
- * run as one single-CTA kernel per V-cycle), pure host arithmetic: -1 = no tail (off, or only the coarsest level fits);
- * a negative GS_E* code below -1 never occurs for valid params */
-int  gs_plan_tail(const gs_params* p, int64_t tail_points);
-
 /* gs_set_option names beyond the four documented in gpusolve_cuda.h (every value gives the same bits; defaults in
  * gpu-solve_b200/csrc/gs_api.cu create_impl):
  *   "smooth_variant", "zchunk", "fast_min_n"   single-sweep kernels (kernels_fast.cu)
  *   "fuse2" = 0 one Jacobi sweep per pass, 1 two sweeps per pass (kernels_fused.cu), "fuse2_min_n", "zchunk2"
  *   "fuse_norm" = 0/1 produce the next pre-smoothing sweeps together with the V-cycle's final residual norm
  *   "unit_taps", "rcp_div", "wave", "vzero" = 0/1 arithmetic / scheduling shortcuts (A/B switches, default 1)
- *   "tail_points" = N: levels of at most N interior points run as one single-CTA kernel per V-cycle (0 = off)
+ *   "fuse_pc" = 0/1 prolongation + correction folded into the first post-smoothing pass (default 1)
  *   "device_stop" = 0/1 inner Newton solves as one conditional CUDA graph with the stopping test on the device
  *   "p2p" = 0/1 slabs: ghost planes pushed through peer-mapped memory instead of NCCL send/recv
  *   "overlap" = 0/1 slabs: ghost refresh on a second stream under the interior of the operator that needs it */

@@ -173,7 +173,7 @@ def test_zchunk_plan_fills_whole_waves(gs, tiles, planes, occ, overhead, lo, hi,
 def test_product_sources_never_touch_the_oracle_or_a_host_compute_path():
     """the oracle is test infrastructure: nothing under the package (library sources, driver, ctypes view) or in the
     public header may include, import, link or name it; and the library exports no host-side compute entry (the
-    __host__ __device__ point functions of kernels_simple.cu are only ever called on the host by tests/tail_host_check.cu)"""
+    __host__ __device__ point functions of kernels_simple.cu are only ever called on the host by tests/pc_host_check.cu)"""
     import re
     pkg = os.path.join(ROOT, "gpu-solve_b200")
     files = [os.path.join(ROOT, "include", "gpusolve_cuda.h"), os.path.join(pkg, "__init__.py"), os.path.join(pkg, "Makefile")]
@@ -185,7 +185,7 @@ def test_product_sources_never_touch_the_oracle_or_a_host_compute_path():
                 assert not pat.search(line), f"{f}:{i} mentions the oracle: {line.strip()}"
     # host code of the library that loops over lattice points would be a CPU path: the only per-point code is device code
     api = open(os.path.join(pkg, "csrc", "gs_api.cu")).read()
-    assert "tail_do_op" not in api and "_point(" not in api
+    assert "_point(" not in api
 
 
 def _check_partition(gs, n, world):
@@ -235,14 +235,3 @@ def test_partition_invariants_on_random_grids(gs):
         _check_partition(gs, n, rnd.randint(2, 8))
 
 
-def test_coarse_tail_selection(gs):
-    """which levels the option "tail_points" hands to the single-CTA kernel (gs_plan_tail, host arithmetic)"""
-    assert gs.plan_tail(gs.make_params(511), 0) == -1                 # off
-    assert gs.plan_tail(gs.make_params(511), 4096) == 5               # 511 255 127 63 31 [15 7 3 1]
-    assert gs.plan_tail(gs.make_params(511), 40000) == 4              # from 31^3
-    assert gs.plan_tail(gs.make_params(127), 4096) == 3               # the shipped config: 127 63 31 [15 7 3 1]
-    assert gs.plan_tail(gs.make_params(15), 4096) == 0                # the whole cycle
-    assert gs.plan_tail(gs.make_params(1), 4096) == -1                # a single level: nothing to merge
-    assert gs.plan_tail(gs.make_params(3), 1) == -1                   # only the coarsest level fits
-    assert gs.plan_tail(gs.make_params((40, 30, 50)), 10000) == 1     # 20 x 15 x 25 = 7500
-    assert gs.plan_tail(gs.make_params(4000), 1 << 20) == 6           # 4000 2000 1000 500 250 125 [62 ...]

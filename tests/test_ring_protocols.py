@@ -19,13 +19,6 @@ def test_resid_restrict_protocol(nzc, ns):
         rm.resid_restrict(nzc, nwarps=4, seed=seed, ns=ns)
 
 
-@pytest.mark.parametrize("nzc", [1, 2, 3, 4, 9, 32])
-def test_resid_restrict_split_phase_protocol(nzc):
-    """rr_variant=2 (prepared): five stages, six residual slots, split-phase barrier"""
-    for seed in range(25):
-        rm.resid_restrict(nzc, nwarps=4, seed=seed, ns=5, sp=True)
-
-
 @pytest.mark.parametrize("nz", [1, 2, 5, 64])
 def test_producer_ring_protocol(nz):
     for seed in range(25):
@@ -37,18 +30,6 @@ def test_model_catches_a_ring_that_is_too_short():
     deadlock hit on the GPU while writing the kernel; RRCfg now static_asserts five stages)"""
     with pytest.raises(rm.Hazard, match="deadlock"):
         rm.resid_restrict(4, ns=4)
-
-
-def test_model_catches_five_slots_under_the_split_phase_barrier():
-    """computing plane 2j+3 before the wait needs the sixth slot: with five it overwrites plane 2j-2 under a slow reader"""
-    hits = 0
-    for seed in range(200):
-        try:
-            rm.resid_restrict(9, seed=seed, ns=5, sp=True, nslot=5)
-        except rm.Hazard as e:
-            assert "slot" in str(e)
-            hits += 1
-    assert hits > 0
 
 
 def test_model_catches_the_zero_input_parity_slip():

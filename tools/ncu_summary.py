@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Summarise an .ncu-rep (read here, no GPU): one line per launch with the roofline-relevant counters.
+"""Summarise an .ncu-rep or its `--page raw --csv` export (read here, no GPU): one line per launch with the roofline-relevant counters.
     python tools/ncu_summary.py gpurun_out/prof.ncu-rep [min_us]"""
 import csv
 import io
@@ -9,7 +9,7 @@ import sys
 
 rep = sys.argv[1]
 min_us = float(sys.argv[2]) if len(sys.argv) > 2 else 0.0
-out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 h, units = rows[0], rows[1]
 cols = {
