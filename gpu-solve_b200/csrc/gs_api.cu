@@ -332,9 +332,10 @@ int slab_z0(const gs_handle* h, int level, int r)
 
 bool use_p2p(const gs_handle* h) { return h->comm && h->opt_p2p && gs_comm_p2p(h->comm); }
 
-// queue the refresh of `depth` ghost planes on both sides of a partitioned level array on stream `s`; with the peer
-// transport the arrival is a separate step (exchange_arrive), which the overlapped path queues after the interior launch
-int exchange_send(gs_handle* h, int level, double* a, int depth, cudaStream_t s)
+// queue the refresh of `depth` ghost planes on both sides of a partitioned level array on stream `s`.  wait = false (peer
+// transport only): the arrival is a separate step (exchange_arrive), which the overlapped path queues after the interior
+// launch; wait = true: push and arrival are one kernel
+int exchange_send(gs_handle* h, int level, double* a, int depth, bool wait, cudaStream_t s)
 {
     Level& L = h->lev[level];
     const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;  // local owned range
@@ -342,7 +343,7 @@ int exchange_send(gs_handle* h, int level, double* a, int depth, cudaStream_t s)
     const int k = use_p2p(h) ? array_slot(h, level, a) : -1;
     if (k >= 0)
         rc = gs_comm_halo_p2p(h->comm, k, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, L.g.z0, slab_z0(h, level, h->rank - 1),
-                              slab_z0(h, level, h->rank + 1), s);
+                              slab_z0(h, level, h->rank + 1), wait, s);
     else rc = gs_comm_halo(h->comm, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, s);
     if (rc != 0) return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
     h->launches += k >= 0 ? 1 : 0;
@@ -362,8 +363,7 @@ int exchange_arrive(gs_handle* h, int level, double* a, cudaStream_t s)
 int exchange_halo(gs_handle* h, int level, double* a, int depth)
 {
     if (!partitioned(h, level)) return GS_OK;
-    GS(exchange_send(h, level, a, depth, h->stream));
-    return exchange_arrive(h, level, a, h->stream);
+    return exchange_send(h, level, a, depth, true, h->stream);
 }
 
 // make `depth` ghost planes of the level's v current (slabs only).  Operators that write v just mark the ghosts
@@ -393,7 +393,7 @@ int halo_begin(gs_handle* h, int level, int band, bool* started)
     if (L.ie - L.ib < (sides + 1) * band) return GS_OK;  // thin slab: plain exchange, one launch
     CU(cudaEventRecord(h->ev_fork, h->stream));
     CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
-    GS(exchange_send(h, level, L.v, 2, h->stream2));
+    GS(exchange_send(h, level, L.v, 2, false, h->stream2));
     GS(exchange_arrive(h, level, L.v, h->stream2));
     CU(cudaEventRecord(h->ev_join, h->stream2));
     *started = true;
@@ -449,7 +449,8 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
         // constant (no memset, no read of v); its output buffer becomes v, the stale one is only ever written again
         L.vzero_next = false;
         bool handled = false;
-        if (iters >= 2 && tuned && !partitioned(h, level))
+        // (slabs: the zero iterate needs no ghost refresh either; f carries its one ghost plane from finish_coarse)
+        if (iters >= 2 && tuned)
             CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, true, &handled));
         if (handled) {
             iters -= 2;
@@ -515,7 +516,7 @@ int norm_to_host(gs_handle* h, int level)
         const int rc = use_p2p(h) ? gs_comm_norm_p2p(h->comm, h->cx.norm.result, h->stream)
                                   : gs_comm_allreduce_sum(h->comm, h->cx.norm.result, 1, h->stream);
         if (rc != 0) return fail(GS_ECOMM, "norm reduction failed: %s", gs_comm_error(h->comm));
-        if (use_p2p(h)) h->launches += 2;
+        if (use_p2p(h)) h->launches += 1;
     }
     CU(cudaMemcpyAsync(h->h_norm, h->cx.norm.result, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     return GS_OK;
@@ -593,7 +594,7 @@ int finish_coarse(gs_handle* h, int level, double* coarse)
         const int rc = k >= 0 ? gs_comm_gather_planes_p2p(h->comm, k, coarse, C.g.plane, level, h->stream)
                               : gs_comm_gather_planes(h->comm, coarse, C.g.plane, level, h->stream);
         if (rc != 0) return fail(GS_ECOMM, "coarse gather failed: %s", gs_comm_error(h->comm));
-        if (k >= 0) h->launches += 2;
+        if (k >= 0) h->launches += 1;
         return GS_OK;
     }
     return exchange_halo(h, level + 1, coarse, 1);
@@ -760,7 +761,7 @@ int enqueue_vcycle(gs_handle* h, bool host_norm = true)
         GS(do_smooth(h, i, h->p.pre));
         GS(do_restrict_residual(h, i));
         if (h->p.mode != GS_MODE_NONLINEAR) {
-            if (h->opt_vzero && h->world == 1) {
+            if (h->opt_vzero) {
                 h->lev[i + 1].vzero_next = true;  // consumed by the do_smooth that follows
                 h->lev[i + 1].pre_valid = 0;
             } else GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));

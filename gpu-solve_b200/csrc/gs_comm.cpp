@@ -357,7 +357,7 @@ void push_header(GsComm* c, P2PPush* q)
 }  // namespace
 
 int gs_comm_halo_p2p(GsComm* c, int k, double* a, long long plane, int lo, int hi, int depth, int zlo, int zhi, int Zg, int z0_me,
-                     int z0_dn, int z0_up, cudaStream_t s)
+                     int z0_dn, int z0_up, bool wait, cudaStream_t s)
 {
     const bool up = c->rank + 1 < c->world && zhi < Zg;
     const bool dn = c->rank > 0 && zlo > 0;
@@ -385,6 +385,7 @@ int gs_comm_halo_p2p(GsComm* c, int k, double* a, long long plane, int lo, int h
         o.dst[0] = peer_array(c, o.rank, k) + (size_t)(z0_me + lo - z0_dn) * plane;
         o.count[0] = cnt;
     }
+    q.wait = wait ? 1 : 0;
     if (kc_p2p_push(q, cnt * q.npeer, c->sm_count, s) != cudaSuccess) {
         c->err = "peer push launch failed";
         return -1;
@@ -417,10 +418,7 @@ int gs_comm_gather_planes_p2p(GsComm* c, int k, double* coarse, long long plane,
     if (ze > Zc - 1) ze = Zc - 1;
     P2PPush q;
     push_header(c, &q);
-    P2PWait w;
-    memset(&w, 0, sizeof w);
-    w.ctl = c->block->ctl;
-    w.err = c->h_err;
+    q.wait = 1;
     const long long cnt = ze > zb ? (long long)(ze - zb) * plane : 0;
     for (int r = 0; r < c->world; r++) {
         if (r == c->rank) continue;
@@ -430,9 +428,8 @@ int gs_comm_gather_planes_p2p(GsComm* c, int k, double* coarse, long long plane,
         o.src[0] = coarse + (size_t)zb * plane;
         o.dst[0] = peer_array(c, r, k) + (size_t)zb * plane;  // replicated level: every rank holds it from plane 0
         o.count[0] = cnt;
-        w.rank[w.npeer++] = r;
     }
-    if (kc_p2p_push(q, cnt * q.npeer, c->sm_count, s) != cudaSuccess || kc_p2p_wait(w, s) != cudaSuccess) {
+    if (kc_p2p_push(q, cnt * q.npeer, c->sm_count, s) != cudaSuccess) {
         c->err = "peer gather launch failed";
         return -1;
     }
@@ -443,10 +440,11 @@ int gs_comm_norm_p2p(GsComm* c, double* dev_result, cudaStream_t s)
 {
     P2PPush q;
     push_header(c, &q);
-    P2PWait w;
-    memset(&w, 0, sizeof w);
-    w.ctl = c->block->ctl;
-    w.err = c->h_err;
+    q.wait = 1;
+    q.norm_slots = c->block->norm_slots;
+    q.norm_result = dev_result;
+    q.world = c->world;
+    q.me = c->rank;
     for (int r = 0; r < c->world; r++) {
         if (r == c->rank) continue;
         P2PPeerOp& o = q.p[q.npeer++];
@@ -455,10 +453,8 @@ int gs_comm_norm_p2p(GsComm* c, double* dev_result, cudaStream_t s)
         o.src[0] = dev_result;
         o.dst[0] = &((P2PBlock*)c->peer_base[r])->norm_slots[c->rank];
         o.count[0] = 1;
-        w.rank[w.npeer++] = r;
     }
-    if (kc_p2p_push(q, 1, c->sm_count, s) != cudaSuccess ||
-        kc_p2p_norm_sum(w, c->block->norm_slots, c->world, c->rank, dev_result, s) != cudaSuccess) {
+    if (kc_p2p_push(q, 1, c->sm_count, s) != cudaSuccess) {
         c->err = "peer norm launch failed";
         return -1;
     }

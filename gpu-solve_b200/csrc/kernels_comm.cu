@@ -14,11 +14,12 @@
 //                3. copy my boundary planes into its ghost planes (16-byte stores to the peer mapping);
 //                4. fence, and the last CTA to finish publishes sig_in = e at the peer and epoch = e here.
 //     p2p_wait   spins until the peer's data of exchange e has landed (sig_in >= epoch); runs right before the consumer.
+//                When nothing is to be overlapped the push kernel does this itself (P2PPush::wait): one launch per exchange.
 //   Both sides send their ack before waiting for the other's, so the handshake cannot deadlock; a spin that exceeds
 //   ~4 s sets an error word instead of hanging the GPU (the host checks it at the next synchronisation).
 // The same two kernels carry the gather of the first replicated coarse level (every rank pushes the coarse planes it
 // computed to all peers) and the residual-norm reduction (one double per rank into every peer's slot array, summed in
-// rank order by p2p_norm_sum: deterministic and bit-identical on all ranks).
+// rank order by the last CTA of the push: deterministic and bit-identical on all ranks).
 #include "gs_comm.h"
 #include "gs_device.cuh"
 
@@ -105,6 +106,17 @@ __global__ void __launch_bounds__(256) p2p_push(P2PPush q)
         const P2PPeerOp& o = q.p[tid];
         st_release_sys(&o.remote->sig_in, e_sh[tid]);
         q.ctl[o.rank].epoch = e_sh[tid];
+        // push + arrival in one launch: the last CTA stays until the peers' data of this exchange has landed here
+        if (q.wait) spin_until(&q.ctl[o.rank].sig_in, e_sh[tid], q.err);
+    }
+    if (q.wait && q.norm_result) {
+        // every rank adds the partial sums in rank order: deterministic and bit-identical on all ranks
+        __syncthreads();
+        if (tid == 0) {
+            double s = 0.0;
+            for (int r = 0; r < q.world; r++) s += (r == q.me) ? *q.norm_result : __ldcg(q.norm_slots + r);
+            *q.norm_result = s;
+        }
     }
     if (tid == 0) *q.ticket = 0u;
 }
@@ -113,20 +125,6 @@ __global__ void p2p_wait(P2PWait w)
 {
     const int tid = threadIdx.x;
     if (tid < w.npeer) spin_until(&w.ctl[w.rank[tid]].sig_in, w.ctl[w.rank[tid]].epoch, w.err);
-}
-
-// after the partial sums of all peers have landed in slots[r] (r != me): *result = sum over ranks in rank order, this
-// rank's own partial being *result itself
-__global__ void p2p_norm_sum(P2PWait w, const double* slots, int world, int me, double* result)
-{
-    const int tid = threadIdx.x;
-    if (tid < w.npeer) spin_until(&w.ctl[w.rank[tid]].sig_in, w.ctl[w.rank[tid]].epoch, w.err);
-    __syncthreads();
-    if (tid == 0) {
-        double s = 0.0;
-        for (int r = 0; r < world; r++) s += (r == me) ? *result : __ldcg(slots + r);
-        *result = s;
-    }
 }
 
 }  // namespace
@@ -144,11 +142,5 @@ cudaError_t kc_p2p_push(const P2PPush& q, long long total_doubles, int sm_count,
 cudaError_t kc_p2p_wait(const P2PWait& w, cudaStream_t s)
 {
     p2p_wait<<<1, 32, 0, s>>>(w);
-    return cudaGetLastError();
-}
-
-cudaError_t kc_p2p_norm_sum(const P2PWait& w, const double* slots, int world, int me, double* result, cudaStream_t s)
-{
-    p2p_norm_sum<<<1, 32, 0, s>>>(w, slots, world, me, result);
     return cudaGetLastError();
 }
