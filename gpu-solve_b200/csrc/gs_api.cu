@@ -71,6 +71,7 @@ struct Level {
     int ar;  // arithmetic flags of the tuned kernels (gs_device.cuh AR_*), same bits either way
     int zlo, zhi;     // owned GLOBAL planes [zlo, zhi) (both physical halo planes belong to the end ranks)
     int ib, ie;       // LOCAL plane range [ib, ie) of owned interior planes
+    int min_interior; // fewest owned interior planes of any rank on this level (= ie - ib on one GPU / replicated levels)
     bool replicated;  // whole level held (and computed) by every rank
     size_t count;     // doubles per array
     double *v, *vtmp, *f, *r, *restV, *newtonV, *coef;
@@ -308,6 +309,11 @@ int smoother_km(const gs_handle* h)
 
 bool partitioned(const gs_handle* h, int level) { return h->world > 1 && !h->lev[level].replicated; }
 
+// Slabs: which kernel runs decides how many ghost refreshes an operator needs, and the refreshes are a handshake between
+// neighbours — so every rank must take the same decision.  The z-marching kernels decline short plane ranges; ask for the
+// fewest planes any rank owns instead of this rank's own count.
+bool slab_planes_ok(const gs_handle* h, int level, int need) { return !partitioned(h, level) || h->lev[level].min_interior >= need; }
+
 // offsets argument of the single-sweep tuned kernels (kernels_fast.cu): null = canonical axis-aligned stencil, else the
 // config's seven offsets (GEN instantiations)
 const StencilOff* gen_offsets(const gs_handle* h) { return h->canonical ? nullptr : &h->so; }
@@ -442,8 +448,8 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     }
     L.pre_valid = 0;
     const double* aux = smoother_aux(h, level, km);
-    const bool tuned1 = h->opt_kernels != 0;
-    const bool tuned = tuned1 && h->canonical;         // two sweeps per pass: canonical stencil only
+    const bool tuned1 = h->opt_kernels != 0 && slab_planes_ok(h, level, 8);
+    const bool tuned = tuned1 && h->canonical && slab_planes_ok(h, level, 16);  // two sweeps per pass: canonical stencil only
     if (L.vzero_next) {
         // CpuSolver.cpp:100-101 v.fill(0) followed by the pre-smoothing: the two-sweep kernel takes the zero iterate as a
         // constant (no memset, no read of v); its output buffer becomes v, the stale one is only ever written again
@@ -551,15 +557,17 @@ int do_norm_residual(gs_handle* h)
         OpScope t(h, GS_OP_RESIDUAL, 0);
         bool handled = false;
         const double* aux = smoother_aux(h, 0, km);
-        GS(need_v_halo(h, 0, (h->p.pre >= 2 && h->cx.tune.fuse2 && h->canonical) ? 2 : 1));
-        if (h->p.pre >= 2 && h->canonical && (!partitioned(h, 0) || L.gv >= 2)) {
+        const bool two = h->p.pre >= 2 && h->canonical && slab_planes_ok(h, 0, 16);
+        GS(need_v_halo(h, 0, (two && h->cx.tune.fuse2) ? 2 : 1));
+        if (two && (!partitioned(h, 0) || L.gv >= 2)) {
             CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, true, false, &handled));
             if (handled) {
                 L.pre_valid = 2;
                 return GS_OK;
             }
         }
-        CU(kf_smooth_norm(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled, gen_offsets(h)));
+        if (slab_planes_ok(h, 0, 8))
+            CU(kf_smooth_norm(h->cx, km, L.ar, L.g, L.ib, L.ie, L.k, L.v, L.vtmp, L.f, aux, &handled, gen_offsets(h)));
         if (handled) {
             L.pre_valid = 1;
             return GS_OK;
@@ -724,7 +732,8 @@ int try_prolong_smooth2(gs_handle* h, int level, bool* done)
     if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
         km == KM_NEWTON_EXP)
         return GS_OK;
-    if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16) return GS_OK;  // kx_smooth2 would decline
+    if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16 || !slab_planes_ok(h, level, 16))
+        return GS_OK;  // kx_smooth2 would decline (on this rank or on another)
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     OpScope t(h, GS_OP_SMOOTH, level);
     // Slabs: the pass needs v + e on two planes outside the slab.  The uncorrected v ghosts are normally still current (the
@@ -1336,6 +1345,10 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
         // owned interior planes, local indices
         L.ib = std::max(1, L.zlo) - g.z0;
         L.ie = std::min(g.nz + 1, L.zhi) - g.z0;
+        L.min_interior = L.ie - L.ib;
+        if (world > 1 && !L.replicated)
+            for (int r = 0; r < world; r++)
+                L.min_interior = std::min(L.min_interior, std::min(g.nz + 1, part.b[l][r + 1]) - std::max(1, part.b[l][r]));
         L.h = 1.0 / (double)(n[1] + 1);  // src/cpu/CpuGridData.cpp:41 (Y dimension)
         PointK& k = L.k;
         for (int i = 0; i < 7; i++) k.c[i] = p->stencil_val[i];
