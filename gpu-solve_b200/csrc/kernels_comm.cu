@@ -74,20 +74,20 @@ __global__ void __launch_bounds__(256) p2p_push(P2PPush q)
             const long long n = o.count[k];
             if (n <= 0) continue;
             if (((n | (long long)(((size_t)src | (size_t)dst) >> 3)) & 1) == 0) {  // even count, 16-byte aligned ends
-                // four independent 16-byte loads in flight per thread before the four remote stores: the copy is bound by
-                // load latency x bytes in flight, and the NVLink stores are fire-and-forget
+                // eight independent 16-byte loads in flight per thread before the eight remote stores: the copy is bound by
+                // load latency x bytes in flight (~10 MB over the grid), and the NVLink stores are fire-and-forget
                 const double2* s2 = reinterpret_cast<const double2*>(src);
                 double2* d2 = reinterpret_cast<double2*>(dst);
                 const long long n2 = n / 2;
                 long long i = gtid;
-                for (; i + 3 * gsz < n2; i += 4 * gsz) {
-                    const double2 a = __ldcs(s2 + i), b = __ldcs(s2 + i + gsz), c = __ldcs(s2 + i + 2 * gsz), d = __ldcs(s2 + i + 3 * gsz);
-                    d2[i] = a;
-                    d2[i + gsz] = b;
-                    d2[i + 2 * gsz] = c;
-                    d2[i + 3 * gsz] = d;
+                for (; i + 7 * gsz < n2; i += 8 * gsz) {
+                    double2 v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) v[u] = __ldcs(s2 + i + u * gsz);
+#pragma unroll
+                    for (int u = 0; u < 8; u++) d2[i + u * gsz] = v[u];
                 }
-                for (; i < n2; i += gsz) d2[i] = s2[i];
+                for (; i < n2; i += gsz) d2[i] = __ldcs(s2 + i);
             } else {
                 for (long long i = gtid; i < n; i += gsz) dst[i] = src[i];
             }
@@ -131,10 +131,9 @@ __global__ void p2p_wait(P2PWait w)
 
 cudaError_t kc_p2p_push(const P2PPush& q, long long total_doubles, int sm_count, cudaStream_t s)
 {
-    // enough CTAs to fill the NVLink pipes, few enough to leave the SMs to a concurrently running interior kernel
-    long long want = (total_doubles / 2 + 255) / 256;
+    // enough CTAs to fill the NVLink pipes (two per SM at most); small exchanges take few CTAs so the handshake stays cheap
+    long long want = (total_doubles / 2 + 256 * 8 - 1) / (256 * 8);
     int grid = (int)(want < 1 ? 1 : (want > 2 * sm_count ? 2 * sm_count : want));
-    if (grid > 128) grid = 128;
     p2p_push<<<grid, 256, 0, s>>>(q);
     return cudaGetLastError();
 }
