@@ -123,9 +123,10 @@ struct gs_handle {
     GsComm* comm;
     Partition part;
     int replicated_from;
-    double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM)
-    size_t stage_count;
-    int opt_overlap;      // slabs: ghost refresh on a second stream, overlapped with the interior of the operator that needs it
+    double* stage;        // device staging buffer of field I/O (flat PCIe transfers, pitch conversion in HBM), two halves
+    size_t stage_count;   // doubles per half
+    cudaStream_t io_stream;        // PCIe copies of field I/O; the pitch conversion runs on `stream`, one chunk behind
+    cudaEvent_t io_copied[2], io_converted[2];
     int opt_fuse_pc;      // prolongation + correction folded into the first post-smoothing pass (kernels_fused.cu PC)
     int opt_p2p;          // slabs: ghost planes, coarse gather and norm through peer-mapped memory (kernels_comm.cu) instead of NCCL
     std::vector<long long> arena_offs;  // byte offset of every registered array in the arena (index level * GS_LEVEL_ARRAYS + slot; last = newtonF)
@@ -135,8 +136,6 @@ struct gs_handle {
     StopCtl* d_stop;      // device-side loop state
     StopCtl* h_stop;      // pinned copy, filled by the graph's last node
     std::map<uint64_t, struct LoopGraph> loops;
-    cudaStream_t stream2;
-    cudaEvent_t ev_fork, ev_join;
 };
 
 namespace {
@@ -338,38 +337,22 @@ int slab_z0(const gs_handle* h, int level, int r)
 
 bool use_p2p(const gs_handle* h) { return h->comm && h->opt_p2p && gs_comm_p2p(h->comm); }
 
-// queue the refresh of `depth` ghost planes on both sides of a partitioned level array on stream `s`.  wait = false (peer
-// transport only): the arrival is a separate step (exchange_arrive), which the overlapped path queues after the interior
-// launch; wait = true: push and arrival are one kernel
-int exchange_send(gs_handle* h, int level, double* a, int depth, bool wait, cudaStream_t s)
+// refresh `depth` ghost planes on both sides of a partitioned level array: one kernel on the peer transport (push +
+// arrival, kernels_comm.cu), a grouped ncclSend/ncclRecv otherwise
+int exchange_halo(gs_handle* h, int level, double* a, int depth)
 {
+    if (!partitioned(h, level)) return GS_OK;
     Level& L = h->lev[level];
     const int lo = L.zlo - L.g.z0, hi = L.zhi - L.g.z0;  // local owned range
     int rc;
     const int k = use_p2p(h) ? array_slot(h, level, a) : -1;
     if (k >= 0)
         rc = gs_comm_halo_p2p(h->comm, k, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, L.g.z0, slab_z0(h, level, h->rank - 1),
-                              slab_z0(h, level, h->rank + 1), wait, s);
-    else rc = gs_comm_halo(h->comm, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, s);
+                              slab_z0(h, level, h->rank + 1), h->stream);
+    else rc = gs_comm_halo(h->comm, a, L.g.plane, lo, hi, depth, L.zlo, L.zhi, L.g.Zg, h->stream);
     if (rc != 0) return fail(GS_ECOMM, "halo exchange failed on level %d: %s", level, gs_comm_error(h->comm));
     h->launches += k >= 0 ? 1 : 0;
     return GS_OK;
-}
-
-int exchange_arrive(gs_handle* h, int level, double* a, cudaStream_t s)
-{
-    if (!use_p2p(h) || array_slot(h, level, a) < 0) return GS_OK;  // NCCL send/recv completes in stream order
-    Level& L = h->lev[level];
-    if (gs_comm_halo_wait_p2p(h->comm, L.zlo, L.zhi, L.g.Zg, s) != 0)
-        return fail(GS_ECOMM, "halo wait failed on level %d: %s", level, gs_comm_error(h->comm));
-    h->launches += 1;
-    return GS_OK;
-}
-
-int exchange_halo(gs_handle* h, int level, double* a, int depth)
-{
-    if (!partitioned(h, level)) return GS_OK;
-    return exchange_send(h, level, a, depth, true, h->stream);
 }
 
 // make `depth` ghost planes of the level's v current (slabs only).  Operators that write v just mark the ghosts
@@ -383,33 +366,6 @@ int need_v_halo(gs_handle* h, int level, int depth)
     const int d = owned >= 2 ? 2 : depth;
     GS(exchange_halo(h, level, L.v, d));
     L.gv = d;
-    return GS_OK;
-}
-
-// Overlapped ghost refresh (opt_overlap, slabs): the exchange of the two ghost planes of v runs on a second stream
-// while the operator runs on the planes that read no ghost; after the join it runs on a band at each side that has a
-// neighbour.  Same kernels and per-point arithmetic, only the plane ranges of the launches differ, so the fields stay
-// bit-identical.  `band` = owned fine planes the operator wants per boundary launch.
-int halo_begin(gs_handle* h, int level, int band, bool* started)
-{
-    *started = false;
-    Level& L = h->lev[level];
-    if (!h->opt_overlap || !partitioned(h, level) || L.gv >= 2 || !h->stream2) return GS_OK;
-    const int sides = (L.zlo > 0 ? 1 : 0) + (L.zhi < L.g.Zg ? 1 : 0);
-    if (L.ie - L.ib < (sides + 1) * band) return GS_OK;  // thin slab: plain exchange, one launch
-    CU(cudaEventRecord(h->ev_fork, h->stream));
-    CU(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
-    GS(exchange_send(h, level, L.v, 2, false, h->stream2));
-    GS(exchange_arrive(h, level, L.v, h->stream2));
-    CU(cudaEventRecord(h->ev_join, h->stream2));
-    *started = true;
-    return GS_OK;
-}
-
-int halo_end(gs_handle* h, int level)
-{
-    CU(cudaStreamWaitEvent(h->stream, h->ev_join, 0));
-    h->lev[level].gv = 2;
     return GS_OK;
 }
 
@@ -470,28 +426,6 @@ int do_smooth(gs_handle* h, int level, uint64_t iters)
     }
     while (iters > 0) {
         bool handled = false;
-        if (iters >= 2 && tuned && h->cx.tune.fuse2) {
-            constexpr int BAND = 16;  // kx_smooth2 takes no shorter range
-            bool started = false;
-            GS(halo_begin(h, level, BAND, &started));
-            if (started) {
-                const int lo_b = L.zlo > 0 ? BAND : 0, hi_b = L.zhi < L.g.Zg ? BAND : 0;
-                CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib + lo_b, L.ie - hi_b, L.k, L.v, L.vtmp, L.f, aux, false, false, &handled));
-                GS(halo_end(h, level));
-                if (handled) {
-                    bool hb = true;
-                    if (lo_b) CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ib, L.ib + lo_b, L.k, L.v, L.vtmp, L.f, aux, false, false, &hb));
-                    if (hi_b && hb) CU(kx_smooth2(h->cx, km, L.ar, L.g, L.ie - hi_b, L.ie, L.k, L.v, L.vtmp, L.f, aux, false, false, &hb));
-                    if (!hb) return fail(GS_ECUDA, "boundary band of the overlapped smoother was not launched (level %d)", level);
-                    iters -= 2;
-                    h->lvl_sweeps[level] += 2;
-                    std::swap(L.v, L.vtmp);
-                    L.gv = 0;
-                    continue;
-                }
-                // the level is too small for the two-sweep kernel: the ghosts are current now, take the plain path
-            }
-        }
         GS(need_v_halo(h, level, (iters >= 2 && tuned && h->cx.tune.fuse2) ? 2 : 1));
         if (iters >= 2 && tuned) {
             // two sweeps per pass (kernels_fused.cu); a slab needs two current ghost planes of v for it
@@ -632,27 +566,6 @@ int do_restrict_residual(gs_handle* h, int level)
     int km = smoother_km(h);
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
     if (partitioned(h, level)) {
-        if (h->opt_kernels && h->canonical) {
-            // overlapped: the coarse planes away from the slab boundaries first, a band of four at each side after the join
-            constexpr int CB = 4;  // kt_resid_restrict takes no shorter range
-            int czb, cze;
-            coarse_range(h, level, &czb, &cze);
-            const int lo_b = L.zlo > 0 ? CB : 0, hi_b = L.zhi < L.g.Zg ? CB : 0;
-            bool started = false;
-            if (cze - czb >= lo_b + hi_b + CB) GS(halo_begin(h, level, 2 * CB, &started));
-            if (started) {
-                bool handled = false;
-                CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb + lo_b, cze - hi_b, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
-                GS(halo_end(h, level));
-                if (handled) {
-                    bool hb = true;
-                    if (lo_b) CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, czb + lo_b, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &hb));
-                    if (hi_b && hb) CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, cze - hi_b, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &hb));
-                    if (!hb) return fail(GS_ECUDA, "boundary band of the overlapped residual+restriction was not launched (level %d)", level);
-                    return finish_coarse(h, level, C.f);
-                }
-            }
-        }
         // the lowest owned coarse plane needs r one fine plane below the slab, which needs v two below
         GS(need_v_halo(h, level, 2));
         if (L.zlo > 0) zb = L.ib - 1;
@@ -1277,6 +1190,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->h_norm = nullptr;
     h->stage = nullptr;
     h->stage_count = 0;
+    h->io_stream = nullptr;
+    for (int b = 0; b < 2; b++) h->io_copied[b] = h->io_converted[b] = nullptr;
     h->arena = nullptr;
     h->arena_bytes = 0;
     h->opt_p2p = 1;
@@ -1287,10 +1202,6 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     if (const char* e = getenv("GPUSOLVE_DEVICE_STOP")) h->opt_device_stop = atoi(e) != 0;
     h->d_stop = nullptr;
     h->h_stop = nullptr;
-    h->opt_overlap = 0;  // prepared, off until it has been through a multi-GPU run
-    h->stream2 = nullptr;
-    h->ev_fork = h->ev_join = nullptr;
-    if (const char* e = getenv("GPUSOLVE_OVERLAP")) h->opt_overlap = atoi(e) != 0;
     memset(h->op_ms, 0, sizeof h->op_ms);
     memset(h->op_launches, 0, sizeof h->op_launches);
     for (int i = 0; i < 7; i++) {
@@ -1458,13 +1369,6 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     }
 
     if (world > 1) {
-        e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
-        if (e != cudaSuccess) {
-            gs_destroy(h);
-            return fail(GS_ECUDA, "second stream setup failed: %s", cudaGetErrorString(e));
-        }
         std::vector<int> bounds;
         for (int l = 0; l < nlev; l++)
             for (int r = 0; r <= world; r++) bounds.push_back(part.b[l][r]);
@@ -1568,6 +1472,11 @@ int gs_destroy(gs_handle* h)
             }
     if (h->newtonF && !h->arena) cudaFree(h->newtonF);
     if (h->arena) cudaFree(h->arena);
+    if (h->io_stream) cudaStreamDestroy(h->io_stream);
+    for (int b = 0; b < 2; b++) {
+        if (h->io_copied[b]) cudaEventDestroy(h->io_copied[b]);
+        if (h->io_converted[b]) cudaEventDestroy(h->io_converted[b]);
+    }
     if (h->stage) cudaFree(h->stage);
     if (h->cx.norm.partials) cudaFree(h->cx.norm.partials);
     if (h->cx.norm.ticket) cudaFree(h->cx.norm.ticket);
@@ -1581,9 +1490,6 @@ int gs_destroy(gs_handle* h)
     }
     for (auto e : h->ev_free) cudaEventDestroy(e);
     if (h->comm) gs_comm_destroy(h->comm);
-    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-    if (h->ev_join) cudaEventDestroy(h->ev_join);
-    if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return GS_OK;
@@ -1629,35 +1535,60 @@ int gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hv
     return GS_OK;
 }
 
-// dense host planes <-> padded device planes through a flat device staging buffer: the PCIe transfer is one
-// contiguous copy per chunk (full link speed), the pitch conversion is a device-to-device 2-D copy in HBM
+// dense host planes <-> padded device planes through a flat device staging buffer: the PCIe transfer is one contiguous
+// copy per chunk (full link speed) on its own stream, the pitch conversion is a device-to-device 2-D copy in HBM on the
+// handle's stream.  The staging buffer has two halves, so the link never waits for a conversion: chunk k+1 crosses PCIe
+// while chunk k is being converted.
 static int staged_copy(gs_handle* h, const Geom& g, double* dev, double* dense, size_t nplanes, bool to_host)
 {
     const size_t XY = (size_t)g.X * g.Y;
-    size_t want = std::max<size_t>(XY, (size_t)8 << 20);  // 64 MB of doubles, or one plane if that is larger
+    size_t want = std::max<size_t>(XY, (size_t)4 << 20);  // 32 MB of doubles per half, or one plane if that is larger
     want = std::min(want, XY * nplanes);
+    if (!h->io_stream) {
+        CU(cudaStreamCreateWithFlags(&h->io_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++) {
+            CU(cudaEventCreateWithFlags(&h->io_copied[b], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->io_converted[b], cudaEventDisableTiming));
+        }
+    }
     if (h->stage_count < want) {
         if (h->stage) cudaFree(h->stage);
         h->stage = nullptr;
         h->stage_count = 0;
-        if (cudaMalloc((void**)&h->stage, want * sizeof(double)) != cudaSuccess)
-            return fail(GS_ENOMEM, "staging buffer of %zu bytes", want * sizeof(double));
+        if (cudaMalloc((void**)&h->stage, 2 * want * sizeof(double)) != cudaSuccess)
+            return fail(GS_ENOMEM, "staging buffer of %zu bytes", 2 * want * sizeof(double));
         h->stage_count = want;
     }
     const size_t ppc = std::max<size_t>(1, h->stage_count / XY);
-    for (size_t p0 = 0; p0 < nplanes; p0 += ppc) {
+    int k = 0;
+    for (size_t p0 = 0; p0 < nplanes; p0 += ppc, k++) {
         const size_t n = std::min(ppc, nplanes - p0);
+        const int b = k & 1;
+        double* st = h->stage + (size_t)b * h->stage_count;
         double* d = dev + GS_XOFF + p0 * (size_t)g.plane;
         double* hp = dense + p0 * XY;
         if (to_host) {
-            CU(cudaMemcpy2DAsync(h->stage, g.X * sizeof(double), d, g.pitch * sizeof(double), g.X * sizeof(double), g.Y * n,
+            if (k >= 2) CU(cudaStreamWaitEvent(h->stream, h->io_copied[b], 0));  // this half has left for the host
+            CU(cudaMemcpy2DAsync(st, g.X * sizeof(double), d, g.pitch * sizeof(double), g.X * sizeof(double), g.Y * n,
                                  cudaMemcpyDeviceToDevice, h->stream));
-            CU(cudaMemcpyAsync(hp, h->stage, n * XY * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaEventRecord(h->io_converted[b], h->stream));
+            CU(cudaStreamWaitEvent(h->io_stream, h->io_converted[b], 0));
+            CU(cudaMemcpyAsync(hp, st, n * XY * sizeof(double), cudaMemcpyDeviceToHost, h->io_stream));
+            CU(cudaEventRecord(h->io_copied[b], h->io_stream));
         } else {
-            CU(cudaMemcpyAsync(h->stage, hp, n * XY * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-            CU(cudaMemcpy2DAsync(d, g.pitch * sizeof(double), h->stage, g.X * sizeof(double), g.X * sizeof(double), g.Y * n,
+            if (k >= 2) CU(cudaStreamWaitEvent(h->io_stream, h->io_converted[b], 0));  // this half has been converted
+            CU(cudaMemcpyAsync(st, hp, n * XY * sizeof(double), cudaMemcpyHostToDevice, h->io_stream));
+            CU(cudaEventRecord(h->io_copied[b], h->io_stream));
+            CU(cudaStreamWaitEvent(h->stream, h->io_copied[b], 0));
+            CU(cudaMemcpy2DAsync(d, g.pitch * sizeof(double), st, g.X * sizeof(double), g.X * sizeof(double), g.Y * n,
                                  cudaMemcpyDeviceToDevice, h->stream));
+            CU(cudaEventRecord(h->io_converted[b], h->stream));
         }
+    }
+    // the caller synchronises h->stream; make that cover the copies on the I/O stream too
+    if (to_host && k > 0) {
+        CU(cudaStreamWaitEvent(h->stream, h->io_copied[(k - 1) & 1], 0));
+        if (k > 1) CU(cudaStreamWaitEvent(h->stream, h->io_copied[k & 1], 0));
     }
     return GS_OK;
 }
@@ -1964,7 +1895,6 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "zchunk") h->cx.tune.zchunk = std::max<int64_t>(1, value);
     else if (n == "fast_min_n") h->cx.tune.fast_min_n = (int)value;
     else if (n == "wave") h->cx.tune.wave = value != 0;
-    else if (n == "overlap") h->opt_overlap = value != 0;
     else if (n == "device_stop") h->opt_device_stop = value != 0;
     else if (n == "p2p") h->opt_p2p = value != 0;
     else if (n == "fuse_pc") h->opt_fuse_pc = value != 0;

@@ -357,7 +357,7 @@ void push_header(GsComm* c, P2PPush* q)
 }  // namespace
 
 int gs_comm_halo_p2p(GsComm* c, int k, double* a, long long plane, int lo, int hi, int depth, int zlo, int zhi, int Zg, int z0_me,
-                     int z0_dn, int z0_up, bool wait, cudaStream_t s)
+                     int z0_dn, int z0_up, cudaStream_t s)
 {
     const bool up = c->rank + 1 < c->world && zhi < Zg;
     const bool dn = c->rank > 0 && zlo > 0;
@@ -385,25 +385,8 @@ int gs_comm_halo_p2p(GsComm* c, int k, double* a, long long plane, int lo, int h
         o.dst[0] = peer_array(c, o.rank, k) + (size_t)(z0_me + lo - z0_dn) * plane;
         o.count[0] = cnt;
     }
-    q.wait = wait ? 1 : 0;
     if (kc_p2p_push(q, cnt * q.npeer, c->sm_count, s) != cudaSuccess) {
         c->err = "peer push launch failed";
-        return -1;
-    }
-    return 0;
-}
-
-int gs_comm_halo_wait_p2p(GsComm* c, int zlo, int zhi, int Zg, cudaStream_t s)
-{
-    P2PWait w;
-    memset(&w, 0, sizeof w);
-    w.ctl = c->block->ctl;
-    w.err = c->h_err;
-    if (c->rank + 1 < c->world && zhi < Zg) w.rank[w.npeer++] = c->rank + 1;
-    if (c->rank > 0 && zlo > 0) w.rank[w.npeer++] = c->rank - 1;
-    if (w.npeer == 0) return 0;
-    if (kc_p2p_wait(w, s) != cudaSuccess) {
-        c->err = "peer wait launch failed";
         return -1;
     }
     return 0;
@@ -418,7 +401,6 @@ int gs_comm_gather_planes_p2p(GsComm* c, int k, double* coarse, long long plane,
     if (ze > Zc - 1) ze = Zc - 1;
     P2PPush q;
     push_header(c, &q);
-    q.wait = 1;
     const long long cnt = ze > zb ? (long long)(ze - zb) * plane : 0;
     for (int r = 0; r < c->world; r++) {
         if (r == c->rank) continue;
@@ -440,7 +422,6 @@ int gs_comm_norm_p2p(GsComm* c, double* dev_result, cudaStream_t s)
 {
     P2PPush q;
     push_header(c, &q);
-    q.wait = 1;
     q.norm_slots = c->block->norm_slots;
     q.norm_result = dev_result;
     q.world = c->world;

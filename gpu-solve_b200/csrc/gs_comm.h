@@ -52,24 +52,16 @@ struct P2PPeerOp {
 };
 struct P2PPush {
     int npeer;
-    int wait;              // 1: the kernel also waits for the peers' data of this exchange (push + arrival in one launch)
     P2PCtl* ctl;           // this rank's control words, indexed by peer rank
     unsigned long long* err;
     unsigned* ticket;
-    // norm reduction (wait = 1): after the arrival, *norm_result = sum over ranks in rank order (own partial = *norm_result)
+    // norm reduction: after the arrival, *norm_result = sum over ranks in rank order (own partial = *norm_result)
     const double* norm_slots;
     double* norm_result;
     int world, me;
     P2PPeerOp p[GS_MAX_PEERS];
 };
-struct P2PWait {
-    int npeer;
-    int rank[GS_MAX_PEERS];
-    P2PCtl* ctl;
-    unsigned long long* err;
-};
 cudaError_t kc_p2p_push(const P2PPush& q, long long total_doubles, int sm_count, cudaStream_t s);
-cudaError_t kc_p2p_wait(const P2PWait& w, cudaStream_t s);
 
 // Map every rank's arena into this process (CUDA IPC; the handles and the per-rank array offsets travel by ncclAllGather).
 // `offs[k]` = byte offset inside the arena of registered array k (the same k names the same logical array on every rank);
@@ -79,11 +71,10 @@ int gs_comm_enable_p2p(GsComm* c, void* arena, size_t arena_bytes, const long lo
 bool gs_comm_p2p(const GsComm* c);
 // the peer-path twins of gs_comm_halo / gs_comm_gather_planes / gs_comm_allreduce_sum.  `k` = registered index of the array
 // `a` points into; z0_dn / z0_up = global plane of LOCAL plane 0 of the neighbour below / above on this level.
-// halo with wait = false: push only (the data is on its way when the kernel ends on this side), halo_wait = the arrival,
-// queued right before the consumer (overlapped refresh); wait = true: push and arrival in ONE launch.
+// Every call is ONE kernel: handshake, push of the boundary planes into the peers' ghost planes, and the wait for the peers'
+// data of the same exchange.
 int gs_comm_halo_p2p(GsComm* c, int k, double* a, long long plane, int lo, int hi, int depth, int zlo, int zhi, int Zg, int z0_me,
-                     int z0_dn, int z0_up, bool wait, cudaStream_t s);
-int gs_comm_halo_wait_p2p(GsComm* c, int zlo, int zhi, int Zg, cudaStream_t s);
+                     int z0_dn, int z0_up, cudaStream_t s);
 int gs_comm_gather_planes_p2p(GsComm* c, int k, double* coarse, long long plane, int fine_level, cudaStream_t s);
 int gs_comm_norm_p2p(GsComm* c, double* dev_result, cudaStream_t s);
 // nonzero once a device-side wait has timed out (checked after synchronising)

@@ -13,11 +13,11 @@
 //                2. wait for the peer's same message (ack_in >= e): now I may overwrite ITS ghost planes;
 //                3. copy my boundary planes into its ghost planes (16-byte stores to the peer mapping);
 //                4. fence, and the last CTA to finish publishes sig_in = e at the peer and epoch = e here.
-//     p2p_wait   spins until the peer's data of exchange e has landed (sig_in >= epoch); runs right before the consumer.
-//                When nothing is to be overlapped the push kernel does this itself (P2PPush::wait): one launch per exchange.
+//                5. that same CTA then spins until the peer's data of exchange e has landed here (sig_in >= e): when the
+//                   kernel ends, the consumer queued behind it may read the ghost planes.  One launch per exchange.
 //   Both sides send their ack before waiting for the other's, so the handshake cannot deadlock; a spin that exceeds
 //   ~4 s sets an error word instead of hanging the GPU (the host checks it at the next synchronisation).
-// The same two kernels carry the gather of the first replicated coarse level (every rank pushes the coarse planes it
+// The same kernel carries the gather of the first replicated coarse level (every rank pushes the coarse planes it
 // computed to all peers) and the residual-norm reduction (one double per rank into every peer's slot array, summed in
 // rank order by the last CTA of the push: deterministic and bit-identical on all ranks).
 #include "gs_comm.h"
@@ -107,9 +107,9 @@ __global__ void __launch_bounds__(256) p2p_push(P2PPush q)
         st_release_sys(&o.remote->sig_in, e_sh[tid]);
         q.ctl[o.rank].epoch = e_sh[tid];
         // push + arrival in one launch: the last CTA stays until the peers' data of this exchange has landed here
-        if (q.wait) spin_until(&q.ctl[o.rank].sig_in, e_sh[tid], q.err);
+        spin_until(&q.ctl[o.rank].sig_in, e_sh[tid], q.err);
     }
-    if (q.wait && q.norm_result) {
+    if (q.norm_result) {
         // every rank adds the partial sums in rank order: deterministic and bit-identical on all ranks
         __syncthreads();
         if (tid == 0) {
@@ -121,12 +121,6 @@ __global__ void __launch_bounds__(256) p2p_push(P2PPush q)
     if (tid == 0) *q.ticket = 0u;
 }
 
-__global__ void p2p_wait(P2PWait w)
-{
-    const int tid = threadIdx.x;
-    if (tid < w.npeer) spin_until(&w.ctl[w.rank[tid]].sig_in, w.ctl[w.rank[tid]].epoch, w.err);
-}
-
 }  // namespace
 
 cudaError_t kc_p2p_push(const P2PPush& q, long long total_doubles, int sm_count, cudaStream_t s)
@@ -135,11 +129,5 @@ cudaError_t kc_p2p_push(const P2PPush& q, long long total_doubles, int sm_count,
     long long want = (total_doubles / 2 + 256 * 8 - 1) / (256 * 8);
     int grid = (int)(want < 1 ? 1 : (want > 2 * sm_count ? 2 * sm_count : want));
     p2p_push<<<grid, 256, 0, s>>>(q);
-    return cudaGetLastError();
-}
-
-cudaError_t kc_p2p_wait(const P2PWait& w, cudaStream_t s)
-{
-    p2p_wait<<<1, 32, 0, s>>>(w);
     return cudaGetLastError();
 }

@@ -27,8 +27,7 @@ int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int ov
  *   "unit_taps", "rcp_div", "wave", "vzero" = 0/1 arithmetic / scheduling shortcuts (A/B switches, default 1)
  *   "fuse_pc" = 0/1 prolongation + correction folded into the first post-smoothing pass (default 1)
  *   "device_stop" = 0/1 inner Newton solves as one conditional CUDA graph with the stopping test on the device
- *   "p2p" = 0/1 slabs: ghost planes pushed through peer-mapped memory instead of NCCL send/recv
- *   "overlap" = 0/1 slabs: ghost refresh on a second stream under the interior of the operator that needs it */
+ *   "p2p" = 0/1 slabs: ghost planes pushed through peer-mapped memory instead of NCCL send/recv */
 
 #ifdef __cplusplus
 }

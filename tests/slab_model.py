@@ -250,11 +250,9 @@ class MgLevel:
 
 
 class SlabMultigrid:
-    def __init__(self, dist, rank, world, n, levels, rep, pre=2, post=2, omega=0.8, overlap=False, mode=0, gamma=1.0):
-        """levels: [(zlo, zhi)] per level from gs_partition; rep: first replicated level; overlap: the ghost refresh
-        runs "beside" the interior launch of the operator that needs it (gs_api.cu halo_begin / halo_end)"""
+    def __init__(self, dist, rank, world, n, levels, rep, pre=2, post=2, omega=0.8, mode=0, gamma=1.0):
+        """levels: [(zlo, zhi)] per level from gs_partition; rep: first replicated level"""
         self.dist, self.rank, self.world = dist, rank, world
-        self.overlap, self.overlapped = overlap, 0
         self.mode, self.gamma = mode, gamma
         self.pre, self.post, self.omega = pre, post, omega
         self.lev = []
@@ -299,59 +297,9 @@ class SlabMultigrid:
         self.exchange(l, L.v, d)
         L.gv = d
 
-    def halo_begin(self, l, band):
-        """may the exchange of level l be overlapped with an interior launch?  If so the ghost planes are poisoned with
-        NaN until halo_end, so that an interior launch that did read them could not go unnoticed"""
-        L = self.lev[l]
-        if not self.overlap or not self.part(l) or L.gv >= 2:
-            return False
-        sides = (1 if L.zlo > 0 else 0) + (1 if L.zhi < L.Z else 0)
-        if L.ie - L.ib < (sides + 1) * band:
-            return False
-        L.v[:L.zlo - L.z0] = np.nan if L.zlo > 0 else L.v[:L.zlo - L.z0]
-        if L.zhi < L.Z:
-            L.v[L.zhi - L.z0:] = np.nan
-        return True
-
-    def halo_end(self, l):
-        L = self.lev[l]
-        self.exchange(l, L.v, 2)
-        L.gv = 2
-        self.overlapped += 1
-
-    def smooth2_range(self, l, zb, ze, out):
-        """one launch of the two-sweep kernel on LOCAL output planes [zb, ze): first sweep on [zb-1, ze+1) clipped to the
-        interior of the level, second on [zb, ze); reads input planes [zb-2, ze+2)"""
-        L = self.lev[l]
-        lo = max(zb - 1, 1 - L.z0)
-        hi = min(ze + 1, L.nz + 1 - L.z0)
-        src = L.v[zb - 2 if zb >= 2 else 0:ze + 2]
-        off = zb - 2 if zb >= 2 else 0
-        kw = dict(mode=self.mode, gamma=self.gamma, aux=L.nv[off:ze + 2])
-        mid, _ = jacobi_sweep(src, L.f[off:ze + 2], L.h, self.omega, lo - off, hi - off, **kw)
-        res, _ = jacobi_sweep(mid, L.f[off:ze + 2], L.h, self.omega, zb - off, ze - off, **kw)
-        out[zb:ze] = res[zb - off:ze - off]
-
     def smooth(self, l, iters):
         L = self.lev[l]
         while iters > 0:
-            if iters >= 2 and self.halo_begin(l, 16):
-                lo_b = 16 if L.zlo > 0 else 0
-                hi_b = 16 if L.zhi < L.Z else 0
-                out = L.v.copy()
-                self.smooth2_range(l, L.ib + lo_b, L.ie - hi_b, out)
-                assert not np.isnan(out[L.ib + lo_b:L.ie - hi_b]).any(), "the interior launch read a ghost plane"
-                self.halo_end(l)
-                if lo_b:
-                    self.smooth2_range(l, L.ib, L.ib + lo_b, out)
-                if hi_b:
-                    self.smooth2_range(l, L.ie - hi_b, L.ie, out)
-                out[:L.ib] = L.v[:L.ib]
-                out[L.ie:] = L.v[L.ie:]
-                L.v = out
-                L.gv = 0
-                iters -= 2
-                continue
             self.need_v_halo(l, 2 if iters >= 2 else 1)
             if iters >= 2 and (not self.part(l) or L.gv >= 2):
                 # two sweeps per pass: the first also updates the ghost plane next to the slab (if it is interior)
@@ -384,20 +332,9 @@ class SlabMultigrid:
             r = residual_planes(F.v, F.f, F.h, rb, re, mode=self.mode, gamma=self.gamma, aux=F.nv)
             C.f[b - C.z0:e - C.z0] = restrict_planes(r, F.z0, b, e, (C.ny + 2, C.nx + 2))
 
-        lo_b = 4 if F.zlo > 0 else 0
-        hi_b = 4 if F.zhi < F.Z else 0
-        if self.part(l) and ce - cb >= lo_b + hi_b + 4 and self.halo_begin(l, 8):
-            launch(cb + lo_b, ce - hi_b)
-            assert not np.isnan(C.f[cb + lo_b - C.z0:ce - hi_b - C.z0]).any(), "the interior launch read a ghost plane"
-            self.halo_end(l)
-            if lo_b:
-                launch(cb, cb + lo_b)
-            if hi_b:
-                launch(ce - hi_b, ce)
-        else:
-            if self.part(l):
-                self.need_v_halo(l, 2)   # the lowest owned coarse plane needs r one fine plane below the slab
-            launch(cb, ce)
+        if self.part(l):
+            self.need_v_halo(l, 2)   # the lowest owned coarse plane needs r one fine plane below the slab
+        launch(cb, ce)
         self.finish_coarse(l, C.f)
 
     def finish_coarse(self, l, coarse):
@@ -471,7 +408,7 @@ class SlabMultigrid:
         return t.item()
 
 
-def vcycle_worker(rank, world, port, n, seed, cycles, out_path, overlap=False, mode=0):
+def vcycle_worker(rank, world, port, n, seed, cycles, out_path, mode=0):
     """gloo process `rank`: `cycles` V(2,2) cycles of a seeded level-0 problem on slabs; rank 0 saves the gathered v"""
     import os
     import sys
@@ -492,7 +429,7 @@ def vcycle_worker(rank, world, port, n, seed, cycles, out_path, overlap=False, m
         for l in range(nlev):
             zlo, zhi, rep = gs.partition(p, world, rank, l)
             levels.append((zlo, zhi))
-        mg = SlabMultigrid(dist, rank, world, n, levels, rep, overlap=overlap, mode=mode)
+        mg = SlabMultigrid(dist, rank, world, n, levels, rep, mode=mode)
         shape = (n + 2, n + 2, n + 2)
         v = seeded_field(shape, seed)
         f = seeded_field(shape, seed + 1, scale=1.0)
@@ -508,6 +445,6 @@ def vcycle_worker(rank, world, port, n, seed, cycles, out_path, overlap=False, m
         if rank == 0:
             parts.sort(key=lambda x: x[0])
             np.savez(out_path, v=np.concatenate([x[2] for x in parts], axis=0), sums=np.array(sums), rep=rep,
-                     exchanges=mg.exchanges, overlapped=mg.overlapped)
+                     exchanges=mg.exchanges)
     finally:
         dist.destroy_process_group()

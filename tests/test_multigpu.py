@@ -1,6 +1,6 @@
 """GPU suite, machines with several GPUs only (skipped on a one-GPU box): the z-slab solver under torchrun against the
 one-GPU solver — fields bit for bit, norms to 1e-12 — with several partitioned levels and, from world = 3 on, ranks that have
-a neighbour on both sides; both transports (peer-mapped memory, NCCL send/recv), with and without the overlapped refresh.
+a neighbour on both sides; both transports (peer-mapped memory, NCCL send/recv).
 And two handles on two devices in one process (per-device kernel setup state)."""
 import os
 import subprocess
@@ -26,7 +26,7 @@ def _torchrun(world, args, env):
     return subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=e)
 
 
-@pytest.mark.parametrize("transport", ["p2p", "nccl", "p2p+overlap", "nccl+overlap"])
+@pytest.mark.parametrize("transport", ["p2p", "nccl"])
 @pytest.mark.parametrize("mode", [0, 1, 2])
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
 def test_slab_solver_equals_one_gpu(gs, world, mode, transport):
@@ -38,8 +38,7 @@ def test_slab_solver_equals_one_gpu(gs, world, mode, transport):
     only_t = os.environ.get("GPUSOLVE_TEST_TRANSPORTS")
     if only_t and transport not in only_t.split(","):
         pytest.skip("transport not selected by GPUSOLVE_TEST_TRANSPORTS")
-    env = {"GPUSOLVE_SLAB_MIN_POINTS": "0", "GPUSOLVE_P2P": "1" if "p2p" in transport else "0",
-           "GPUSOLVE_OVERLAP": "1" if "overlap" in transport else "0"}
+    env = {"GPUSOLVE_SLAB_MIN_POINTS": "0", "GPUSOLVE_P2P": "1" if transport == "p2p" else "0"}
     pre = "3" if mode == 2 else "2"
     r = _torchrun(world, ["--grid", "255", "--mode", str(mode), "--cycles", "2", "--pre", pre, "--post", pre], env)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])

@@ -82,27 +82,6 @@ def test_slab_vcycles_over_gloo_equal_whole_grid_oracle(oracle_mod, tmp_path, mo
     o.close()
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_overlapped_ghost_refresh_keeps_the_bits(oracle_mod, tmp_path, monkeypatch, world):
-    """gs_api.cu halo_begin / halo_end (option "overlap"): the operator runs on the planes that read no ghost while the
-    exchange is in flight, then on a band at each side with a neighbour.  In the model the ghosts are NaN until the
-    exchange "arrives", so a wrong band bound cannot hide; the fields must equal the whole-grid oracle bit for bit"""
-    import torch.multiprocessing as mp
-    n = 127
-    monkeypatch.setenv("GPUSOLVE_SLAB_MIN_POINTS", "1000")
-    out = str(tmp_path / "mg.npz")
-    mp.spawn(slab_model.vcycle_worker, args=(world, _free_port(), n, 41, 1, out, True), nprocs=world, join=True)
-    got = np.load(out)
-    assert int(got["overlapped"]) > 0, "nothing was overlapped"
-    o = oracle_mod.Oracle(oracle_mod.make_params(n, mode=0, pre=2, post=2, maxiter=1, tol=1e-30), "port")
-    shape = o.shape(0)
-    o.set(0, V, seeded_field(shape, 41))
-    o.set(0, F, seeded_field(shape, 42, scale=1.0))
-    o.vcycle()
-    assert np.array_equal(got["v"], o.get(0, V))
-    o.close()
-
-
 @pytest.mark.parametrize("mode", [1, 2])
 def test_slab_vcycles_in_the_exp_modes(oracle_mod, tmp_path, monkeypatch, mode):
     """FAS (two-output restriction, coarse right-hand side from restV, v -= restV before the prolongation) and the Newton
@@ -115,7 +94,7 @@ def test_slab_vcycles_in_the_exp_modes(oracle_mod, tmp_path, monkeypatch, mode):
     outs = []
     for world in (3, 1):
         out = str(tmp_path / f"mg{world}.npz")
-        mp.spawn(slab_model.vcycle_worker, args=(world, _free_port(), n, 41, cycles, out, False, mode), nprocs=world, join=True)
+        mp.spawn(slab_model.vcycle_worker, args=(world, _free_port(), n, 41, cycles, out, mode), nprocs=world, join=True)
         outs.append(np.load(out))
     assert int(outs[0]["rep"]) >= 2 and int(outs[1]["rep"]) == 0
     assert np.array_equal(outs[0]["v"], outs[1]["v"]), "sharding changed the bits"
