@@ -645,6 +645,9 @@ int try_prolong_smooth2(gs_handle* h, int level, bool* done)
     if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
         km == KM_NEWTON_EXP)
         return GS_OK;
+    // With exp() in the sweeps (mode 1) the fused pass runs out of registers and loses to the two separate passes
+    // (2.31 ms against 1.64 + 0.44 at 513^3, profiles/r02k_levels_mode1.txt): fuse_pc = 2 forces it for A/B
+    if (km == KM_NONLINEAR && h->opt_fuse_pc < 2) return GS_OK;
     if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16 || !slab_planes_ok(h, level, 16))
         return GS_OK;  // kx_smooth2 would decline (on this rank or on another)
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
@@ -1197,7 +1200,7 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->opt_p2p = 1;
     if (const char* e = getenv("GPUSOLVE_P2P")) h->opt_p2p = atoi(e) != 0;
     h->opt_fuse_pc = 1;  // validated on the GPU (profiles/r02a_*): same bits, one pass per level and cycle fewer
-    if (const char* e = getenv("GPUSOLVE_FUSE_PC")) h->opt_fuse_pc = atoi(e) != 0;
+    if (const char* e = getenv("GPUSOLVE_FUSE_PC")) h->opt_fuse_pc = std::max(0, std::min(2, atoi(e)));
     h->opt_device_stop = 1;
     if (const char* e = getenv("GPUSOLVE_DEVICE_STOP")) h->opt_device_stop = atoi(e) != 0;
     h->d_stop = nullptr;
@@ -1897,7 +1900,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "device_stop") h->opt_device_stop = value != 0;
     else if (n == "p2p") h->opt_p2p = value != 0;
-    else if (n == "fuse_pc") h->opt_fuse_pc = value != 0;
+    else if (n == "fuse_pc") h->opt_fuse_pc = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;
         for (auto& L : h->lev) L.ar = level_ar(L, h->opt_unit != 0, h->opt_rcp_div != 0);

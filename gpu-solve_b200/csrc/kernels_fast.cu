@@ -268,8 +268,15 @@ __global__ void __launch_bounds__(TX* TY + 32) stencil_tma(const __grid_constant
         for (int i = 0; i < 7; i++) goff[i] = ctr + p.gdy[i] * Cfg::VW + p.gdx[i];
     }
 
+    // the Newton coefficient / iterate is the one operand outside the TMA ring: fetched one plane ahead into a register and
+    // three planes ahead into L2, so no step waits a DRAM round trip for it (70 % of the stalls before, profiles/r02a_ncu_modes_summary.txt)
+    double aux_next = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
     for (int q = 1; q <= nz; q++) {
-        const double aux = (KM >= KM_NEWTON_EXP) ? p.aux[c] : 0.0;
+        const double aux = aux_next;
+        if (KM >= KM_NEWTON_EXP) {
+            if (q < nz) aux_next = p.aux[c + p.g.plane];
+            if (q + 3 <= nz) prefetch_l2(p.aux + c + 3 * p.g.plane);
+        }
         mbar_wait(&full[(q + 1) % NSTAGE], ((q + 1) / NSTAGE) & 1);
         const double* vb = vbox(q);
         const double U = vbox(q + 1)[ctr];

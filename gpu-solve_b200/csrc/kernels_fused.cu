@@ -398,6 +398,15 @@ __global__ void __launch_bounds__(S2uCfg<TY>::THREADS, 2) smooth2u_tma(const __g
         if (KM >= KM_NEWTON_EXP) {
             if (a1 && zok) xa = xp[0];
             if (b1 && zok) xb = xp[ab];
+            // the coefficient is the one operand that does not come through the TMA ring: without help every step waits a
+            // DRAM round trip for it (52 % of the stalls, profiles/r02a_ncu_modes_summary.txt).  Next plane into L1, the
+            // plane three ahead into L2; no register is held meanwhile.
+            if (a1 && q + 3 <= qhi) {
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + plane));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + plane + ab));
+                prefetch_l2(xp + 3 * plane);
+                prefetch_l2(xp + 3 * plane + ab);
+            }
         }
         const uint32_t c = tb + SC * Cfg::STAGE, u = tb + SU * Cfg::STAGE;
         double Ea = 0.0, Wa = 0.0, Sa = 0.0, Eb = 0.0, Wb = 0.0, Nb = 0.0;

@@ -25,7 +25,7 @@ int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int ov
  *   "fuse2" = 0 one Jacobi sweep per pass, 1 two sweeps per pass (kernels_fused.cu), "fuse2_min_n", "zchunk2"
  *   "fuse_norm" = 0/1 produce the next pre-smoothing sweeps together with the V-cycle's final residual norm
  *   "unit_taps", "rcp_div", "wave", "vzero" = 0/1 arithmetic / scheduling shortcuts (A/B switches, default 1)
- *   "fuse_pc" = 0/1 prolongation + correction folded into the first post-smoothing pass (default 1)
+ *   "fuse_pc" = 0/1/2 prolongation + correction folded into the first post-smoothing pass (default 1: modes 0 and 2; 2: mode 1 too)
  *   "device_stop" = 0/1 inner Newton solves as one conditional CUDA graph with the stopping test on the device
  *   "p2p" = 0/1 slabs: ghost planes pushed through peer-mapped memory instead of NCCL send/recv */
 

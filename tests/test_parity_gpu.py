@@ -365,7 +365,7 @@ def test_prolongation_folded_into_the_post_smoother_keeps_the_bits(gs, mode, n, 
         per_run = u.launches - l0
         u.close()
         b = CudaBackend(gs, kernels=1, graph=graph, **kw)
-        b.set_option("fuse_pc", 1)
+        b.set_option("fuse_pc", 2)   # 2: also in mode 1, where the default keeps the separate passes (slower fused)
         for rep in range(2):
             l0 = b.launches
             norms, v = run(b)
