@@ -92,6 +92,7 @@ SIGNATURES = {
     "gs_destroy": (_i, [_vp]),
     "gs_partition": (_i, [C.POINTER(Params), _i, _i, _i, C.POINTER(_u64), C.POINTER(_u64), C.POINTER(_i)]),
     "gs_plan_zchunk": (_i, [_i, _i, _i, _i, _i, _i, _i, _i]),
+    "gs_time_halo_exchange": (_i, [C.c_void_p, _i, _i, _i, C.POINTER(C.c_double)]),
     "gs_num_levels": (_i, [_vp]),
     "gs_get_level_info": (_i, [_vp, _i, C.POINTER(_u64 * 3), _dp]),
     "gs_get_field": (_i, [_vp, _i, _i, _vp, _i]),
@@ -303,6 +304,12 @@ class GpuSolve:
     @property
     def stream(self):
         return self.lib.gs_stream(self.h)
+
+    def time_halo_exchange(self, level, depth=2, reps=20):
+        """slabs: ms per ghost-plane refresh of the level's v (collective)"""
+        ms = C.c_double()
+        _check(self.lib.gs_time_halo_exchange(self.h, level, depth, reps, C.byref(ms)))
+        return ms.value
 
     def synchronize(self):
         _check(self.lib.gs_synchronize(self.h))

@@ -1523,6 +1523,32 @@ int gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int ove
     return gs_pick_zchunk_waves(cx, tiles, planes, ctas_per_sm, overhead, min_chunk, max_chunk, even != 0);
 }
 
+// measurement hook (gpusolve_cuda_tuning.h): `reps` ghost-plane refreshes of the level's v, `depth` planes deep, back to
+// back on the handle's stream; *ms_per_exchange = CUDA-event time / reps.  Collective on slabs; GS_EINVAL if the level is
+// not partitioned.  The ghost planes receive what they already hold, so the fields do not change.
+int gs_time_halo_exchange(gs_handle* h, int level, int depth, int reps, double* ms_per_exchange)
+{
+    GS(check_level(h, level));
+    if (!partitioned(h, level) || depth < 1 || depth > 2 || reps < 1) return fail(GS_EINVAL, "level %d is not partitioned (or bad depth / reps)", level);
+    CU(cudaSetDevice(h->device));
+    Level& L = h->lev[level];
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    GS(exchange_halo(h, level, L.v, depth));  // warm-up
+    CU(cudaEventRecord(a, h->stream));
+    for (int i = 0; i < reps; i++) GS(exchange_halo(h, level, L.v, depth));
+    CU(cudaEventRecord(b, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    if (h->comm && gs_comm_p2p_failed(h->comm)) return fail(GS_ECOMM, "a peer did not arrive at a ghost-plane exchange within the time limit");
+    if (ms_per_exchange) *ms_per_exchange = ms / reps;
+    return GS_OK;
+}
+
 int gs_num_levels(const gs_handle* h) { return h ? (int)h->lev.size() : fail(GS_EINVAL, "null handle"); }
 
 int gs_get_level_info(const gs_handle* h, int level, uint64_t dim[3], double* hval)

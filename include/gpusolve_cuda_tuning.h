@@ -19,6 +19,10 @@ extern "C" {
 int  gs_plan_zchunk(int tiles, int planes, int sm_count, int ctas_per_sm, int overhead,
                     int min_chunk, int max_chunk, int even);
 
+/* slabs: time `reps` back-to-back refreshes of `depth` (1 or 2) ghost planes of the level's v (CUDA events on the handle's
+ * stream, after one warm-up); collective, the fields do not change.  *ms_per_exchange = time / reps. */
+int  gs_time_halo_exchange(gs_handle* h, int level, int depth, int reps, double* ms_per_exchange);
+
 /* gs_set_option names beyond the four documented in gpusolve_cuda.h (every value gives the same bits; defaults in
  * gpu-solve_b200/csrc/gs_api.cu create_impl):
  *   "smooth_variant", "zchunk", "fast_min_n"   single-sweep kernels (kernels_fast.cu)
