@@ -8,6 +8,9 @@
 #pragma once
 #include <cuda.h>
 
+#include <string.h>
+#include <math.h>
+
 #include <atomic>
 #include <mutex>
 
@@ -105,6 +108,96 @@ enum { AR_POW2 = 1, AR_UNIT = 2, AR_RCP = 4 };
 #define GS_FMA(a, b, c) fma(a, b, c)
 #endif
 
+// ---------------------------------------------------------------------------------
+// exp() and the per-point divide of the non-linear modes
+// ---------------------------------------------------------------------------------
+// The exp() modes are instruction-bound (profiles/r02a_ncu_modes_summary.txt: 68 % of the issue slots, DRAM 27 %), and a
+// third of what they issue is the library exp / divide moving immediates into registers and testing special cases.
+// gs_exp: k = rint(x / ln 2), r = x - k ln 2 (two-part ln 2), Taylor polynomial of degree 13 on |r| <= 0.347 (truncation
+// 4e-18, below 1 ulp in total; tests/test_exp_div.py measures it against glibc), scaled by 2^k through the exponent
+// field; arguments outside +-700 (and NaN) go to the library.  North_star's tolerance for these modes is 1e-12 relative;
+// CUDA's own exp differs from glibc's by up to an ulp as well.
+GS_HD double gs_bits_to_double(long long b)
+{
+#ifdef __CUDA_ARCH__
+    return __longlong_as_double(b);
+#else
+    double d;
+    memcpy(&d, &b, 8);
+    return d;
+#endif
+}
+GS_HD long long gs_double_to_bits(double d)
+{
+#ifdef __CUDA_ARCH__
+    return __double_as_longlong(d);
+#else
+    long long b;
+    memcpy(&b, &d, 8);
+    return b;
+#endif
+}
+
+// the special cases stay out of line: one copy per kernel, not one per call site of an unrolled loop
+__host__ __device__ __noinline__ inline double gs_exp_library(double x) { return exp(x); }
+__host__ __device__ __noinline__ inline double gs_div_library(double a, double b) { return a / b; }
+
+// coefficients as constant-bank operands of the fma (an immediate double costs two moves into uniform registers each time)
+#define GS_EXP_TABLE                                                                                     \
+    {1.6059043836821613e-10, /* 1/13! */ 2.0876756987868100e-09, /* 1/12! */ 2.5052108385441720e-08,     \
+     2.7557319223985890e-07, /* 1/10! */ 2.7557319223985893e-06, /* 1/9! */ 2.4801587301587302e-05,      \
+     1.9841269841269841e-04, /* 1/7! */ 1.3888888888888889e-03, /* 1/6! */ 8.3333333333333332e-03,       \
+     4.1666666666666664e-02, /* 1/4! */ 1.6666666666666666e-01, /* 1/3! */ 0.5, 1.0,                     \
+     1.4426950408889634074,        /* [13] log2(e) */                                                    \
+     6755399441055744.0,           /* [14] 2^52 + 2^51: the integer lands in the low mantissa bits */    \
+     -6.93147180369123816490e-01,  /* [15] -ln2, high part */                                            \
+     -1.90821492927058770002e-10}  /* [16] -ln2, low part */
+static __constant__ double gs_exp_c[17] = GS_EXP_TABLE;
+static const double gs_exp_c_host[17] = GS_EXP_TABLE;
+#ifdef __CUDA_ARCH__
+#define GS_EXP_C(i) gs_exp_c[i]
+#else
+#define GS_EXP_C(i) gs_exp_c_host[i]
+#endif
+
+GS_HD double gs_exp(double x)
+{
+    if (!(fabs(x) < 700.0)) return gs_exp_library(x);
+    const double t = GS_FMA(x, GS_EXP_C(13), GS_EXP_C(14));
+    const double kd = t - GS_EXP_C(14);
+    const long long k = (long long)(int)(unsigned)gs_double_to_bits(t);
+    double r = GS_FMA(kd, GS_EXP_C(15), x);
+    r = GS_FMA(kd, GS_EXP_C(16), r);
+    double p = GS_EXP_C(0);
+#pragma unroll
+    for (int i = 1; i <= 12; i++) p = GS_FMA(p, r, GS_EXP_C(i));
+    p = GS_FMA(p, r, 1.0);
+    return p * gs_bits_to_double((k + 1023) << 52);  // |x| < 700: k + 1023 in [13, 2033], a normal exponent
+}
+
+// a / b for the Jacobi update of the exp() modes (b = c0/h^2 + gamma (1 + w) e^w, a normal number in any run that has not
+// already diverged): reciprocal seed refined by two Newton steps, quotient corrected once by its exact remainder — the
+// sequence of the library's divide without its scaling of extreme exponents; operands outside the safe exponent range go
+// to the library.  The result is the correctly rounded quotient except for rare last-bit cases (tests/test_exp_div.py).
+GS_HD double gs_div(double a, double b)
+{
+    const double ab = fabs(b), aa = fabs(a);
+    if (!(ab > 1e-280 && ab < 1e280 && aa < 1e280)) return gs_div_library(a, b);
+#ifdef __CUDA_ARCH__
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(b));
+#else
+    double y = gs_bits_to_double(gs_double_to_bits(1.0 / b) & ~0xffffffffll);  // the seed's precision: upper mantissa bits only
+#endif
+    double e = GS_FMA(-b, y, 1.0);
+    y = GS_FMA(y, e, y);
+    e = GS_FMA(-b, y, 1.0);
+    y = GS_FMA(y, e, y);
+    double q = a * y;
+    const double rem = GS_FMA(-b, q, a);
+    return GS_FMA(rem, y, q);
+}
+
 // s / (h*h) under the level's arithmetic flags; every branch returns the same bits
 template <int AR>
 GS_HD double div_hh(double s, const PointK& k)
@@ -126,12 +219,12 @@ GS_HD double finish_residual(double s, double vc, double fc, double aux, const P
     s = div_hh<AR>(s, k);
     den = 0.0;
     if (KM == KM_NONLINEAR) {
-        double ex = exp(vc);
+        double ex = gs_exp(vc);
         double nl = (k.gamma * vc) * ex;
         s += nl;
         den = k.preFac + (k.gamma * (1 + vc)) * ex;
     } else if (KM == KM_NEWTON_EXP) {
-        double ex = exp(aux);
+        double ex = gs_exp(aux);
         double g1 = k.gamma * (1 + aux);
         s += (g1 * vc) * ex;
         den = k.preFac + g1 * ex;
@@ -149,7 +242,7 @@ GS_HD double jacobi_update(double vc, double r, double den, const PointK& k)
 {
     // src/cpu/CpuSolver.cpp:158 resp. :164,:171
     if (KM == KM_LINEAR) return vc + k.omega * (k.alpha * r);
-    return vc + k.omega * (r / den);
+    return vc + k.omega * gs_div(r, den);
 }
 
 // ---------------------------------------------------------------------------------

@@ -575,19 +575,39 @@ cudaError_t launch_s2u(const LaunchCtx& cx, Fused2P p, bool* handled)
 template <int KM, int AR, bool NORM>
 cudaError_t dispatch_s2(const LaunchCtx& cx, const Fused2P& p, int variant, bool vzero, bool pc, bool* handled)
 {
+    // Tile height: 12 rows (448 threads, 72 registers at two CTAs per SM); with the per-point Newton coefficient the state
+    // no longer fits and spills, so that mode takes 10 rows (384 threads, 80 registers): 3.01 against 3.14 ms for the three
+    // level-0 smoother launches of a V(3,3) cycle at 513^3, while modes 0 and 1 lose 6 % and 2 % with the smaller tile
+    // (profiles/r02m_tile_height.txt).  tune.s2_ty forces one or the other for A/B (preparation calls set up both).
+    constexpr int TYD = KM == KM_NEWTON_COEF ? 10 : 12;
+    const int ty = !p.vin ? 0 : (cx.tune.s2_ty == 10 || cx.tune.s2_ty == 12) ? cx.tune.s2_ty : TYD;
+    cudaError_t e = cudaSuccess;
+#define GS_S2U(NORMV, VZV, PCV)                                                                             \
+    do {                                                                                                    \
+        if (ty == 0 || ty == 12) e = launch_s2u<KM, AR, NORMV, 12, VZV, PCV>(cx, p, handled);               \
+        if (e == cudaSuccess && (ty == 0 || ty == 10)) e = launch_s2u<KM, AR, NORMV, 10, VZV, PCV>(cx, p, handled); \
+    } while (0)
     if (pc) {  // prolongation + correction folded in: the unrolled kernel only, no norm, a real input iterate
-        if (variant == 1 || KM == KM_NEWTON_EXP || NORM || vzero) return cudaSuccess;
-        return launch_s2u<KM, AR, false, 12, false, true>(cx, p, handled);
+        if (variant == 1 || vzero) return cudaSuccess;
+        if constexpr (KM == KM_NEWTON_EXP || NORM) return cudaSuccess;
+        else {
+            GS_S2U(false, false, true);
+            return e;
+        }
     }
     // the unrolled kernel spills heavily with exp() of the Newton iterate in the loop (KM_NEWTON_EXP, only reached
     // with the precomputed-coefficient path switched off): that mode keeps the rolled kernel
     if (variant == 1 || KM == KM_NEWTON_EXP) return vzero ? cudaSuccess : launch_s2<KM, AR, NORM, 14, 5>(cx, p, handled);
-    // the zero-input variant exists where the V-cycle zeroes the coarse iterate: modes 0 and 2, no norm wanted
-    if (vzero) {
-        if (!NORM && (KM == KM_LINEAR || KM == KM_NEWTON_COEF)) return launch_s2u<KM, AR, false, 12, true>(cx, p, handled);
-        return cudaSuccess;
+    if constexpr (KM != KM_NEWTON_EXP) {
+        // the zero-input variant exists where the V-cycle zeroes the coarse iterate: modes 0 and 2, no norm wanted
+        if (vzero) {
+            if constexpr (!NORM && (KM == KM_LINEAR || KM == KM_NEWTON_COEF)) GS_S2U(false, true, false);
+            return e;
+        }
+        GS_S2U(NORM, false, false);
     }
-    return launch_s2u<KM, AR, NORM, 12, false>(cx, p, handled);
+#undef GS_S2U
+    return e;
 }
 
 }  // namespace

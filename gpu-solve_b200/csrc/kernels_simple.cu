@@ -206,7 +206,7 @@ GS_HD void fas_rhs_point(const Geom& g, const PointK& k, const i64 (&toff)[7], c
     const double vc = restv[c];
     double s = tap_sum(restv, c, k.c, toff);
     s = POW2 ? s * k.inv_hh : s / k.hh;
-    const double nl = (k.gamma * vc) * exp(vc);
+    const double nl = (k.gamma * vc) * gs_exp(vc);
     s += nl;
     if (r_out) r_out[c] = s;
     f[c] = f[c] + s;
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(BX* BY) newton_F_simple(NewtonFP p)
         const double vc = p.nv[c];
         double s = tap_sum(p.nv, c, p.k.c, p.toff);
         s = POW2 ? s * p.k.inv_hh : s / p.k.hh;
-        const double ex = exp(vc);
+        const double ex = gs_exp(vc);
         const double nl = (p.k.gamma * vc) * ex;
         s += nl;
         const double fv = p.newtonF[c] - s;
@@ -263,7 +263,7 @@ GS_HD void newton_coef_point(const Geom& g, double gamma, const double* nv, doub
 {
     const i64 c = gs_idx(g, x, y, zl);
     const double n = nv[c];
-    coef[c] = (gamma * (1 + n)) * exp(n);
+    coef[c] = (gamma * (1 + n)) * gs_exp(n);
 }
 
 __global__ void __launch_bounds__(BX* BY) newton_coef_simple(Geom g, int zb, double gamma, const double* __restrict__ nv,
@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(BX* BY) init_rhs_simple(Geom g, int mode, doub
         const double px = x * h, py = y * h, pz = zg * h;
         const double val = 2.0 * ((py - py * py) * (pz - pz * pz) + (px - px * px) * (pz - pz * pz) + (px - px * px) * (py - py * py)) +
                            gamma * (px - px * px) * (py - py * py) * (pz - pz * pz) *
-                               exp((px - px * px) * (py - py * py) * (pz - pz * pz));
+                               gs_exp((px - px * px) * (py - py * py) * (pz - pz * pz));
         f[gs_idx(g, x, y, zl)] = val;
     }
 }
