@@ -527,6 +527,28 @@ def main():
                         "the pass also carries the prolongation) / average launch time, CUDA events inside the V-cycle; frac is a bandwidth "
                         "fraction.  The pass applies sweeps_per_launch Jacobi sweeps: glups and lup_equivalent_gbs (24 B per lattice "
                         "UPDATE, SURVEY 8d) carry that"}
+    if fused_pc and world == 1:
+        # what the fused pass replaces, measured in the same run: prolongation + correction and the two post-sweeps as two passes
+        try:
+            solver.set_option("fuse_pc", 0)
+            ums, _, _ = job.time_cycles(solver, max(3, min(args.steps, 10)), 3)
+            _, ull, ulm, _ = per_level_profile(solver, 3)
+            solver.set_option("fuse_pc", 1)
+            u_s = ulm[0].get("smooth", 0.0) / max(ull[0].get("smooth", 1.0), 1e-9)
+            u_p = ulm[0].get("prolong", 0.0)
+            roofline["replaces"] = {
+                "passes": "prolong_correct_zmarch (17 B per point) + smooth2u_tma (24 B per point), option fuse_pc = 0",
+                "prolong_ms": u_p, "smooth2_ms": u_s, "smooth2_frac": 24.0 * P[0] / max(u_s * 1e-3, 1e-12) / 1e9 / peak,
+                "prolong_frac": 17.0 * P[0] / max(u_p * 1e-3, 1e-12) / 1e9 / peak,
+                "vcycle_ms_unfused": ums, "vcycle_ms_fused": ms_per_step,
+                "note": "the fused pass moves 25 B per point where the two it replaces move 41; it is latency-bound (coarse-value loads, "
+                        "one step less TMA lead), so its own bandwidth fraction is lower than either of theirs while the cycle is faster"}
+        except Exception as ex:  # never cost the line
+            roofline["replaces"] = {"error": repr(ex)}
+            try:
+                solver.set_option("fuse_pc", 1)
+            except Exception:
+                pass
     vbytes = vcycle_algorithmic_bytes(n, pre, post)
     launched_bytes = pass_level_bytes(n, 0, ll)
 

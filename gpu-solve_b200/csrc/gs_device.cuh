@@ -162,7 +162,8 @@ static const double gs_exp_c_host[17] = GS_EXP_TABLE;
 
 GS_HD double gs_exp(double x)
 {
-    if (!(fabs(x) < 700.0)) return gs_exp_library(x);
+    // |x| >= 700, infinities and NaN: one integer compare on the high word (an fp64 compare costs two issue cycles)
+    if ((unsigned)((gs_double_to_bits(x) >> 32) & 0x7fffffff) >= 0x4085E000u) return gs_exp_library(x);
     const double t = GS_FMA(x, GS_EXP_C(13), GS_EXP_C(14));
     const double kd = t - GS_EXP_C(14);
     const long long k = (long long)(int)(unsigned)gs_double_to_bits(t);
@@ -181,8 +182,9 @@ GS_HD double gs_exp(double x)
 // to the library.  The result is the correctly rounded quotient except for rare last-bit cases (tests/test_exp_div.py).
 GS_HD double gs_div(double a, double b)
 {
-    const double ab = fabs(b), aa = fabs(a);
-    if (!(ab > 1e-280 && ab < 1e280 && aa < 1e280)) return gs_div_library(a, b);
+    // exponents: b within 2^-930 .. 2^930, a below 2^930 (zeros, infinities and NaN fail the test); integer compares
+    const unsigned eb = (unsigned)(gs_double_to_bits(b) >> 52) & 0x7ffu, ea = (unsigned)(gs_double_to_bits(a) >> 52) & 0x7ffu;
+    if (eb - 93u > 1860u || ea > 1953u) return gs_div_library(a, b);
 #ifdef __CUDA_ARCH__
     double y;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(b));
