@@ -38,27 +38,17 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
 
 constexpr long long SPIN_LIMIT = 1ll << 33;  // clock64 ticks (~4.4 s at 1.9 GHz)
 
-__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p)
-{
-    unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-
-// returns false on timeout.  Polls with relaxed loads (the flag lives in this GPU's memory; the peer's store lands in its
-// L2) and takes the acquire once, after the flag has been seen.
+// returns false on timeout
 __device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long want, unsigned long long* err)
 {
-    if (ld_relaxed_sys(flag) < want) {
-        const long long t0 = clock64();
-        while (ld_relaxed_sys(flag) < want) {
-            if (clock64() - t0 > SPIN_LIMIT) {
-                *err = 1ull;
-                return false;
-            }
+    const long long t0 = clock64();
+    while (ld_acquire_sys(flag) < want) {
+        if (clock64() - t0 > SPIN_LIMIT) {
+            *err = 1ull;
+            return false;
         }
+        __nanosleep(64);
     }
-    asm volatile("fence.acq_rel.sys;" ::: "memory");
     return true;
 }
 
@@ -103,17 +93,15 @@ __global__ void __launch_bounds__(256) p2p_push(P2PPush q)
             }
         }
     }
-    // one system-scope fence per CTA, after the CTA barrier that collects every thread's stores (cumulativity carries them),
-    // instead of one per thread: a fence.sys drains the NVLink writes and thousands of them queue up
+    __threadfence_system();
     __syncthreads();
     if (tid == 0) {
-        __threadfence_system();
         const unsigned t = atomicAdd(q.ticket, 1u);
         last = (t == gridDim.x - 1);
-        if (last) __threadfence_system();  // every CTA's ticket (and the stores its fence ordered before it) observed
     }
     __syncthreads();
     if (!last) return;
+    __threadfence_system();
     if (tid < q.npeer) {
         const P2PPeerOp& o = q.p[tid];
         st_release_sys(&o.remote->sig_in, e_sh[tid]);
