@@ -161,12 +161,10 @@ def smooth2u(nzo, nwarps=4, seed=0, vz=False, ns=6, plain_arrive=True):
 
 
 # ---------------------------------------------------------------------------------
-# resid_restrict_tma (kernels_transfer.cu): thread-0 issue after the per-coarse-plane barrier; sp = split-phase variant
+# resid_restrict_tma (kernels_transfer.cu): thread-0 issue after the per-coarse-plane barrier
 # ---------------------------------------------------------------------------------
-def resid_restrict(nzc, nwarps=4, seed=0, ns=6, sp=False, early_first=False, nslot=None, refill_ahead=0):
-    nslot = nslot or (6 if sp else 5)
+def resid_restrict(nzc, nwarps=4, seed=0, ns=6, nslot=5, refill_ahead=0):
     sim = Sim(ns, nslot, nwarps, seed)
-    rbar = MBar(nwarps)
     nvp = 2 * nzc + 3
     nxt = [0]
 
@@ -201,31 +199,13 @@ def resid_restrict(nzc, nwarps=4, seed=0, ns=6, sp=False, early_first=False, nsl
             yield None
 
         yield from do_plane(0)
-        if not sp:
-            for j in range(nzc):
-                yield from do_plane(2 * j + 1)
-                yield from do_plane(2 * j + 2)
-                yield sim.cta_barrier(w)
-                if w == 0:
-                    refill(j)
-                yield from restrict(j)
-        else:
-            yield from do_plane(1)
-            yield from do_plane(2)
-            rbar.arrive()
-            for j in range(nzc):
-                more = j + 1 < nzc
-                if more and (j > 0 or early_first):
-                    yield from do_plane(2 * j + 3)
-                yield _wait(rbar, j & 1)
-                if w == 0:
-                    refill(j)
-                yield from restrict(j)
-                if more:
-                    if j == 0 and not early_first:
-                        yield from do_plane(3)
-                    yield from do_plane(2 * j + 4)
-                    rbar.arrive()
+        for j in range(nzc):
+            yield from do_plane(2 * j + 1)
+            yield from do_plane(2 * j + 2)
+            yield sim.cta_barrier(w)
+            if w == 0:
+                refill(j)
+            yield from restrict(j)
 
     sim.run([warp(w) for w in range(nwarps)])
     return sim

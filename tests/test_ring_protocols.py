@@ -50,20 +50,6 @@ def test_model_catches_a_refill_that_runs_ahead():
     assert hits > 0
 
 
-def test_split_phase_first_iteration_cannot_run_ahead_with_five_stages():
-    """why the kernel skips the early plane at j = 0: v plane 5 is only requested by the refill behind the first wait"""
-    with pytest.raises(rm.Hazard, match="deadlock"):
-        rm.resid_restrict(4, ns=5, sp=True, early_first=True)
-    for seed in range(10):
-        rm.resid_restrict(4, seed=seed, ns=6, sp=True, early_first=True)   # a sixth stage would allow it
-
-
-@pytest.mark.parametrize("nzo", [1, 2, 5, 6, 7, 13, 40])
-def test_design_study_prolongation_folded_into_the_smoother(nzo):
-    """next round's fusion: correcting plane q+2 in place at step q needs no new barrier ..."""
-    for seed in range(25):
-        rm.smooth2_prolong(nzo, seed=seed)
-
 
 def test_design_study_correcting_one_plane_ahead_is_a_race():
     """... whereas correcting plane q+1 at step q lets a fast warp read a neighbour's point before it was corrected"""
