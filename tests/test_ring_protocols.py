@@ -49,9 +49,14 @@ def test_model_catches_a_refill_that_runs_ahead():
             hits += 1
     assert hits > 0
 
+@pytest.mark.parametrize("nzo", [1, 2, 5, 6, 7, 13, 40])
+def test_prolongation_folded_into_the_smoother(nzo):
+    """smooth2u_tma<PC> (kernels_fused.cu): correcting plane q+2 in place at step q needs no new barrier ..."""
+    for seed in range(25):
+        rm.smooth2_prolong(nzo, seed=seed)
 
 
-def test_design_study_correcting_one_plane_ahead_is_a_race():
+def test_correcting_one_plane_ahead_is_a_race():
     """... whereas correcting plane q+1 at step q lets a fast warp read a neighbour's point before it was corrected"""
     hits = 0
     for seed in range(100):
