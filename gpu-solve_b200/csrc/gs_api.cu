@@ -1358,6 +1358,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->cx.tune.rr_variant = 1;  // six-stage ring
     h->cx.tune.fuse2 = 1;
     h->cx.tune.fuse2_min_n = 96;
+    h->cx.tune.pdl = 1;
+    if (const char* ev = getenv("GPUSOLVE_PDL")) h->cx.tune.pdl = atoi(ev) != 0;
     h->cx.tune.s2_ty = 0;
     if (const char* ev = getenv("GPUSOLVE_S2_TY")) h->cx.tune.s2_ty = atoi(ev);
     h->cx.tune.zchunk2 = 128;
@@ -1937,6 +1939,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
         h->lev[0].pre_valid = 0;
     } else if (n == "fuse2_min_n") h->cx.tune.fuse2_min_n = (int)value;
+    else if (n == "pdl") h->cx.tune.pdl = value != 0;
     else if (n == "s2_ty") h->cx.tune.s2_ty = (int)value;
     else if (n == "zchunk2") h->cx.tune.zchunk2 = (int)std::max<int64_t>(8, value);
     else return fail(GS_EINVAL, "unknown option \"%s\"", name);

@@ -12,6 +12,7 @@
 #include <math.h>
 
 #include <atomic>
+#include <utility>
 #include <mutex>
 
 #include "gs_internal.h"
@@ -107,6 +108,39 @@ enum { AR_POW2 = 1, AR_UNIT = 2, AR_RCP = 4 };
 #else
 #define GS_FMA(a, b, c) fma(a, b, c)
 #endif
+
+// ---------------------------------------------------------------------------------
+// programmatic dependent launch (sm_90+)
+// ---------------------------------------------------------------------------------
+// A V-cycle is a chain of ~50 dependent kernels; on the levels below 48 points per axis they take a few microseconds each
+// and the chain is bound by the launch-to-launch latency of the graph.  A kernel launched with the attribute may be made
+// resident while its predecessor still runs; it first tells its own successor to come (launch_dependents) and then waits for
+// the predecessor's completion and memory flush (wait) before it touches anything, so the dependency itself is unchanged.
+// Used by the one-thread-per-point kernels (kernels_simple.cu): graph V-cycle 0.125 -> 0.111 ms at 63^3, 0.177 -> 0.163 at
+// 127^3, 0.471 -> 0.445 at 255^3 (profiles/r02r_pdl.txt).  On the large-shared-memory TMA kernels it gained nothing at 513^3
+// and lost at the small sizes (early-resident CTAs hold 108 KB each), so those are launched plainly.  Without the attribute
+// (option pdl = 0) both instructions are no-ops.
+__device__ __forceinline__ void gs_pdl_sync()
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+template <typename... KArgs, typename... Args>
+cudaError_t gs_launch(const LaunchCtx& cx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = cx.stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = cx.tune.pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 // ---------------------------------------------------------------------------------
 // exp() and the per-point divide of the non-linear modes

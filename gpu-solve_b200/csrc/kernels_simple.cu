@@ -15,6 +15,8 @@
 
 namespace {
 
+
+
 constexpr int BX = 64, BY = 4;  // 256 threads, one x-row of 64 points per 2 warps
 
 struct SmoothP {
@@ -55,6 +57,7 @@ GS_HD void smooth_point(const Geom& g, const PointK& k, const i64 (&toff)[7], co
 template <int KM, bool POW2>
 __global__ void __launch_bounds__(BX* BY) smooth_simple(SmoothP p)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + p.zb;
@@ -92,6 +95,7 @@ GS_HD double residual_point(const Geom& g, const PointK& k, const i64 (&toff)[7]
 template <int KM, bool POW2>
 __global__ void __launch_bounds__(BX* BY) residual_simple(ResidP p)
 {
+    gs_pdl_sync();
     __shared__ double sh[32];
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
@@ -139,6 +143,7 @@ GS_HD void restrict_point(const Geom& gf, const Geom& gc, const double* fine, do
 
 __global__ void __launch_bounds__(BX* BY) restrict_simple(RestrictP p)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zc = blockIdx.z + p.zb;  // local coarse plane
@@ -180,6 +185,7 @@ GS_HD void prolong_correct_point(const Geom& gf, const Geom& gc, const double* v
 
 __global__ void __launch_bounds__(BX* BY) prolong_correct_simple(ProlongP p)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + p.zb;
@@ -215,6 +221,7 @@ GS_HD void fas_rhs_point(const Geom& g, const PointK& k, const i64 (&toff)[7], c
 template <bool POW2>
 __global__ void __launch_bounds__(BX* BY) fas_rhs_simple(FasP p)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + p.zb;
@@ -237,6 +244,7 @@ struct NewtonFP {
 template <bool POW2>
 __global__ void __launch_bounds__(BX* BY) newton_F_simple(NewtonFP p)
 {
+    gs_pdl_sync();
     __shared__ double sh[32];
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
@@ -269,6 +277,7 @@ GS_HD void newton_coef_point(const Geom& g, double gamma, const double* nv, doub
 __global__ void __launch_bounds__(BX* BY) newton_coef_simple(Geom g, int zb, double gamma, const double* __restrict__ nv,
                                                               double* __restrict__ coef)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + zb;
@@ -287,6 +296,7 @@ GS_HD void axpy_point(const Geom& g, double* dst, const double* src, int sign, i
 __global__ void __launch_bounds__(BX* BY) axpy_simple(Geom g, int zb, double* __restrict__ dst, const double* __restrict__ src,
                                                        int sign)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x + 1;
     const int y = blockIdx.y * BY + threadIdx.y + 1;
     const int zl = blockIdx.z + zb;
@@ -308,6 +318,7 @@ __device__ __forceinline__ double rhs_f2(double x)
 // interior index (:47-58).  Otherwise: whole array, sampled at the array index (:62-76).
 __global__ void __launch_bounds__(BX* BY) init_rhs_simple(Geom g, int mode, double h, double gamma, double* __restrict__ f)
 {
+    gs_pdl_sync();
     const int x = blockIdx.x * BX + threadIdx.x;
     const int y = blockIdx.y * BY + threadIdx.y;
     const int zl = blockIdx.z;
@@ -355,23 +366,25 @@ cudaError_t ks_copy(const LaunchCtx& cx, double* dst, const double* src, size_t 
     return cudaMemcpyAsync(dst, src, count * sizeof(double), cudaMemcpyDeviceToDevice, cx.stream);
 }
 
-#define KM_DISPATCH(KERNEL, km, pow2, ...)                                                          \
-    do {                                                                                            \
-        if (pow2) {                                                                                 \
-            switch (km) {                                                                           \
-            case KM_LINEAR: KERNEL<KM_LINEAR, true> __VA_ARGS__; break;                             \
-            case KM_NONLINEAR: KERNEL<KM_NONLINEAR, true> __VA_ARGS__; break;                       \
-            case KM_NEWTON_EXP: KERNEL<KM_NEWTON_EXP, true> __VA_ARGS__; break;                     \
-            default: KERNEL<KM_NEWTON_COEF, true> __VA_ARGS__; break;                               \
-            }                                                                                       \
-        } else {                                                                                    \
-            switch (km) {                                                                           \
-            case KM_LINEAR: KERNEL<KM_LINEAR, false> __VA_ARGS__; break;                            \
-            case KM_NONLINEAR: KERNEL<KM_NONLINEAR, false> __VA_ARGS__; break;                      \
-            case KM_NEWTON_EXP: KERNEL<KM_NEWTON_EXP, false> __VA_ARGS__; break;                    \
-            default: KERNEL<KM_NEWTON_COEF, false> __VA_ARGS__; break;                              \
-            }                                                                                       \
-        }                                                                                           \
+#define KM_DISPATCH(KERNEL, km, pow2, P)                                                                    \
+    do {                                                                                                    \
+        cudaError_t le__ = cudaSuccess;                                                                     \
+        if (pow2) {                                                                                         \
+            switch (km) {                                                                                   \
+            case KM_LINEAR: le__ = gs_launch(cx, KERNEL<KM_LINEAR, true>, grid, block, 0, P); break;       \
+            case KM_NONLINEAR: le__ = gs_launch(cx, KERNEL<KM_NONLINEAR, true>, grid, block, 0, P); break; \
+            case KM_NEWTON_EXP: le__ = gs_launch(cx, KERNEL<KM_NEWTON_EXP, true>, grid, block, 0, P); break; \
+            default: le__ = gs_launch(cx, KERNEL<KM_NEWTON_COEF, true>, grid, block, 0, P); break;         \
+            }                                                                                               \
+        } else {                                                                                            \
+            switch (km) {                                                                                   \
+            case KM_LINEAR: le__ = gs_launch(cx, KERNEL<KM_LINEAR, false>, grid, block, 0, P); break;      \
+            case KM_NONLINEAR: le__ = gs_launch(cx, KERNEL<KM_NONLINEAR, false>, grid, block, 0, P); break; \
+            case KM_NEWTON_EXP: le__ = gs_launch(cx, KERNEL<KM_NEWTON_EXP, false>, grid, block, 0, P); break; \
+            default: le__ = gs_launch(cx, KERNEL<KM_NEWTON_COEF, false>, grid, block, 0, P); break;        \
+            }                                                                                               \
+        }                                                                                                   \
+        if (le__ != cudaSuccess) return le__;                                                               \
     } while (0)
 
 cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
@@ -381,7 +394,7 @@ cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int
     SmoothP p{g, k, {}, zb, vin, vout, f, aux};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
-    KM_DISPATCH(smooth_simple, km, pow2, <<<grid, block, 0, cx.stream>>>(p));
+    KM_DISPATCH(smooth_simple, km, pow2, p);
     return done(cx);
 }
 
@@ -393,7 +406,7 @@ cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
     if ((size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaErrorInvalidValue;
-    KM_DISPATCH(residual_simple, km, pow2, <<<grid, block, 0, cx.stream>>>(p));
+    KM_DISPATCH(residual_simple, km, pow2, p);
     return done(cx);
 }
 
@@ -402,7 +415,7 @@ cudaError_t ks_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int
 {
     if (ze <= zb || gc.nx <= 0 || gc.ny <= 0) return cudaSuccess;
     RestrictP p{gf, gc, zb, fine, coarse, coarse2};
-    restrict_simple<<<grid_for(gc.nx, gc.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
+    if (cudaError_t le = gs_launch(cx, restrict_simple, grid_for(gc.nx, gc.ny, ze - zb), dim3(BX, BY), 0, p)) return le;
     return done(cx);
 }
 
@@ -411,7 +424,7 @@ cudaError_t ks_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
 {
     if (ze <= zb) return cudaSuccess;
     ProlongP p{gf, gc, zb, vin, vout, coarse, e_out};
-    prolong_correct_simple<<<grid_for(gf.nx, gf.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(p);
+    if (cudaError_t le = gs_launch(cx, prolong_correct_simple, grid_for(gf.nx, gf.ny, ze - zb), dim3(BX, BY), 0, p)) return le;
     return done(cx);
 }
 
@@ -422,8 +435,7 @@ cudaError_t ks_fas_rhs(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, in
     FasP p{g, k, {}, zb, restv, f, r_out};
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
-    if (pow2) fas_rhs_simple<true><<<grid, block, 0, cx.stream>>>(p);
-    else fas_rhs_simple<false><<<grid, block, 0, cx.stream>>>(p);
+    if (cudaError_t le = pow2 ? gs_launch(cx, fas_rhs_simple<true>, grid, block, 0, p) : gs_launch(cx, fas_rhs_simple<false>, grid, block, 0, p)) return le;
     return done(cx);
 }
 
@@ -435,27 +447,26 @@ cudaError_t ks_newton_F(const LaunchCtx& cx, bool pow2, const Geom& g, int zb, i
     fill_toff(g, so, p.toff);
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
     if ((size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaErrorInvalidValue;
-    if (pow2) newton_F_simple<true><<<grid, block, 0, cx.stream>>>(p);
-    else newton_F_simple<false><<<grid, block, 0, cx.stream>>>(p);
+    if (cudaError_t le = pow2 ? gs_launch(cx, newton_F_simple<true>, grid, block, 0, p) : gs_launch(cx, newton_F_simple<false>, grid, block, 0, p)) return le;
     return done(cx);
 }
 
 cudaError_t ks_newton_coef(const LaunchCtx& cx, const Geom& g, int zb, int ze, double gamma, const double* nv, double* coef)
 {
     if (ze <= zb) return cudaSuccess;
-    newton_coef_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, gamma, nv, coef);
+    if (cudaError_t le = gs_launch(cx, newton_coef_simple, grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, g, zb, gamma, nv, coef)) return le;
     return done(cx);
 }
 
 cudaError_t ks_axpy(const LaunchCtx& cx, const Geom& g, int zb, int ze, double* dst, const double* src, int sign)
 {
     if (ze <= zb) return cudaSuccess;
-    axpy_simple<<<grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, cx.stream>>>(g, zb, dst, src, sign);
+    if (cudaError_t le = gs_launch(cx, axpy_simple, grid_for(g.nx, g.ny, ze - zb), dim3(BX, BY), 0, g, zb, dst, src, sign)) return le;
     return done(cx);
 }
 
 cudaError_t ks_init_rhs(const LaunchCtx& cx, const Geom& g, int mode, double h, double gamma, double* f)
 {
-    init_rhs_simple<<<grid_for(g.X, g.Y, g.nzl), dim3(BX, BY), 0, cx.stream>>>(g, mode, h, gamma, f);
+    if (cudaError_t le = gs_launch(cx, init_rhs_simple, grid_for(g.X, g.Y, g.nzl), dim3(BX, BY), 0, g, mode, h, gamma, f)) return le;
     return done(cx);
 }
