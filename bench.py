@@ -675,12 +675,12 @@ def main():
                       "sweeps_per_pass": msw / max(spn, 1e-9), "glups": msw * P[0] / max(mlm[0].get("smooth", 1e-9) * 1e-3, 1e-12) / 1e9,
                       "vcycle_pass_level_bytes": lb, "vcycle_frac_of_peak": lb / (ms * 1e-3) / 1e9 / peak, "per_operator": pop,
                       "binds": ("instruction issue, not memory: exp + divide per point per sweep (gs_exp / gs_div: a degree-13 polynomial and "
-                                "a Newton-refined reciprocal without the library's special-case scaffolding); with the library calls the "
-                                "pass sat at 68 % of the issue slots and 55 % of the fp64 pipe with DRAM at 27 % "
-                                "(ncu: profiles/r02a_ncu_modes_summary.txt, smooth2u_tma<1,...>)" if mode == 1 else
-                                "latency and the divide (no pipe saturated): DRAM 40 %, issue 51 %, fp64 36 % for the two-sweep pass, 32 B per "
+                                "a Newton-refined reciprocal without the library's special-case scaffolding): 65 % of the fp64 pipe, 64 % of the "
+                                "issue slots, DRAM 30 %, dependency waits the largest stall (ncu: profiles/r02aa_ncu_modes_summary.txt, "
+                                "smooth2u_tma<1,...>; with the library calls 55 % / 68 % / 27 %, profiles/r02a_ncu_modes_summary.txt)" if mode == 1 else
+                                "latency and the divide (no pipe saturated): DRAM 49 %, issue 62 %, fp64 41 % for the two-sweep pass, 32 B per "
                                 "point with the precomputed coefficient and one divide per point per sweep; the single-sweep pass of V(3,3) "
-                                "reaches DRAM 64 % (ncu: profiles/r02a_ncu_modes_summary.txt, smooth2u_tma<3,...> / stencil_tma<3,...>)")}
+                                "reaches DRAM 79 % (ncu: profiles/r02aa_ncu_modes_summary.txt, smooth2u_tma<3,...> / stencil_tma<3,...>)")}
               # the shipped examples/data-2nd_order.conf (BASELINE configs[0]): Newton, 127^3, V(3,3) — ms per Newton iteration
               p = gs.make_params(127, mode=2, pre=3, post=3, maxiter=10, tol=1e-5)
               s = gs.GpuSolve(p, device=job.local)
