@@ -645,9 +645,11 @@ int try_prolong_smooth2(gs_handle* h, int level, bool* done)
     if (!h->opt_fuse_pc || !h->opt_kernels || !h->canonical || !h->cx.tune.fuse2 || h->p.post < 2 || flip ||
         km == KM_NEWTON_EXP)
         return GS_OK;
-    // With exp() in the sweeps (mode 1) the fused pass runs out of registers and loses to the two separate passes
-    // (2.31 ms against 1.64 + 0.44 at 513^3, profiles/r02k_levels_mode1.txt): fuse_pc = 2 forces it for A/B
-    if (km == KM_NONLINEAR && h->opt_fuse_pc < 2) return GS_OK;
+    // Only the linear mode gains: with exp() in the sweeps (mode 1) or the per-point coefficient (mode 2) the fused pass runs
+    // out of registers and loses to the two separate passes at 513^3 — mode 1: 2.31 ms against 1.64 + 0.44; mode 2, V(3,3)
+    // cycle 5.61 against 5.46 ms, V(2,2) 4.04 against 3.82 (profiles/r02k_levels_mode1_fuse_pc.txt, r02ad_fuse_pc_mode2.txt).
+    // fuse_pc = 2 forces it in every mode for A/B and for the parity test.
+    if (km != KM_LINEAR && h->opt_fuse_pc < 2) return GS_OK;
     if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16 || !slab_planes_ok(h, level, 16))
         return GS_OK;  // kx_smooth2 would decline (on this rank or on another)
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));

@@ -29,7 +29,7 @@ int  gs_time_halo_exchange(gs_handle* h, int level, int depth, int reps, double*
  *   "fuse2" = 0 one Jacobi sweep per pass, 1 two sweeps per pass (kernels_fused.cu), "fuse2_min_n", "zchunk2"
  *   "fuse_norm" = 0/1 produce the next pre-smoothing sweeps together with the V-cycle's final residual norm
  *   "unit_taps", "rcp_div", "wave", "vzero" = 0/1 arithmetic / scheduling shortcuts (A/B switches, default 1)
- *   "fuse_pc" = 0/1/2 prolongation + correction folded into the first post-smoothing pass (default 1: modes 0 and 2; 2: mode 1 too)
+ *   "fuse_pc" = 0/1/2 prolongation + correction folded into the first post-smoothing pass (default 1: linear mode only; 2: every mode)
  *   "device_stop" = 0/1 inner Newton solves as one conditional CUDA graph with the stopping test on the device
  *   "pdl" = 0/1 small-level kernels launched with programmatic stream serialization (default 1)
  *   "s2_ty" = 0/10/12 tile height of the two-sweep kernel (0: per mode)
