@@ -100,6 +100,7 @@ SIGNATURES = {
     "gs_dump_field": (_i, [_vp, _i, _i, C.c_char_p]),
     "gs_smooth": (_i, [_vp, _i, _u64]),
     "gs_residual": (_i, [_vp, _i, _dp]),
+    "gs_residual_static": (_i, [_vp, _i, _dp]),
     "gs_restrict": (_i, [_vp, _i, _i, _i]),
     "gs_restrict_residual": (_i, [_vp, _i]),
     "gs_fas_coarse_rhs": (_i, [_vp, _i]),
@@ -230,6 +231,12 @@ class GpuSolve:
     def residual(self, level):
         n = C.c_double()
         _check(self.lib.gs_residual(self.h, level, C.byref(n)))
+        return n.value
+
+    def residual_static(self, level):
+        """gs_residual with the reduction scratch in static device memory: nothing on the call path allocates"""
+        n = C.c_double()
+        _check(self.lib.gs_residual_static(self.h, level, C.byref(n)))
         return n.value
 
     def restrict(self, level, src, dst):

@@ -1726,6 +1726,32 @@ int gs_residual(gs_handle* h, int level, double* norm)
     return GS_OK;
 }
 
+// gs_residual without any allocation on the call path (include/gpusolve_cuda.h): the one-thread-per-point residual kernel
+// with its reduction scratch in a static __device__ array (kernels_simple.cu ks_residual_static), the result read back
+// through the pinned word the handle already owns.  No cudaMalloc / cudaFree / allocating library call from here down.
+int gs_residual_static(gs_handle* h, int level, double* norm)
+{
+    GS(check_level(h, level));
+    CU(cudaSetDevice(h->device));
+    if (partitioned(h, level))
+        return fail(GS_EUNSUPPORTED, "gs_residual_static: level %d is split into slabs (the norm would need the peer exchange); use gs_residual", level);
+    Level& L = h->lev[level];
+    const size_t ctas = ks_residual_ctas(L.g, L.ie - L.ib);
+    if (ctas > (size_t)GS_STATIC_SCRATCH_MAX_CTAS)
+        return fail(GS_EINVAL,
+                    "gs_residual_static: level %d (%d x %d x %d) needs %zu reduction slots, the static scratch holds %d "
+                    "(ceil(nx/64) * ceil(ny/4) * nz <= %d, e.g. up to 255^3); use gs_residual",
+                    level, L.g.nx, L.g.ny, L.g.nz, ctas, GS_STATIC_SCRATCH_MAX_CTAS, GS_STATIC_SCRATCH_MAX_CTAS);
+    const int km = smoother_km(h);
+    if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));  // a kernel into an array allocated by gs_create
+    double* res_dev = nullptr;
+    CU(ks_residual_static(h->cx, km, L.pow2, L.g, L.ib, L.ie, L.k, h->so, L.v, L.f, smoother_aux(h, level, km), L.r, &res_dev));
+    CU(cudaMemcpyAsync(h->h_norm, res_dev, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (norm) *norm = sqrt(*h->h_norm);
+    return GS_OK;
+}
+
 int gs_restrict(gs_handle* h, int level, int src_field, int dst_field)
 {
     GS(check_level(h, level));

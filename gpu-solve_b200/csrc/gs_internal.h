@@ -100,6 +100,17 @@ cudaError_t ks_smooth(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int
 // r = f - A(v) (stored if r != nullptr) and sum of squares -> cx.norm.result
 cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
                         const StencilOff& so, const double* v, const double* f, const double* aux, double* r);
+// No-allocation variant of ks_residual (gs_residual_static, no counterpart in
+// the reference): the per-CTA partial sums, the ticket and the result of the norm reduction live in a file-scope static
+// __device__ array of kernels_simple.cu instead of the handle's cudaMalloc'ed NormBuf.  Calls nothing that allocates.
+// *result_dev receives the DEVICE address of the sum of squares (valid once the stream has run the kernel).  The launch
+// needs ks_residual_ctas(g, ze - zb) <= GS_STATIC_SCRATCH_MAX_CTAS reduction slots (else cudaErrorInvalidValue).
+// Every call on a device shares the one array: calls that overlap on the GPU race.
+constexpr int GS_STATIC_SCRATCH_MAX_CTAS = 65536;  // 512 KB of partial sums per GPU that loads the library
+size_t ks_residual_ctas(const Geom& g, int planes);
+cudaError_t ks_residual_static(const LaunchCtx& cx, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                               const StencilOff& so, const double* v, const double* f, const double* aux, double* r,
+                               double** result_dev);
 // coarse(interior) = full weighting of fine; coarse local planes [zb, ze)
 cudaError_t ks_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zb, int ze, const double* fine,
                         double* coarse, double* coarse2);

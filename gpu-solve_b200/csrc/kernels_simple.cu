@@ -11,6 +11,8 @@
 // CUDA-vs-glibc exp rounding only.
 #include <string.h>
 
+#include <mutex>
+
 #include "gs_device.cuh"
 
 namespace {
@@ -407,6 +409,61 @@ cudaError_t ks_residual(const LaunchCtx& cx, int km, bool pow2, const Geom& g, i
     dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
     if ((size_t)grid.x * grid.y * grid.z > cx.norm.cap) return cudaErrorInvalidValue;
     KM_DISPATCH(residual_simple, km, pow2, p);
+    return done(cx);
+}
+
+// ---------------------------------------------------------------------------------
+// residual + norm with the reduction scratch in static device memory (gs_internal.h ks_residual_static)
+// ---------------------------------------------------------------------------------
+// Layout of the array: [0, MAX) one partial sum per CTA, [MAX] the result, [MAX + 1] the ticket (its first four bytes).
+// In HOST code the name g_static_norm_scratch is only a stand-in for the symbol, not a device address: the address is asked
+// for once per device, with that device current, by cudaGetSymbolAddress below.
+static __device__ __align__(256) double g_static_norm_scratch[GS_STATIC_SCRATCH_MAX_CTAS + 2];
+
+size_t ks_residual_ctas(const Geom& g, int planes)
+{
+    if (planes <= 0 || g.nx <= 0 || g.ny <= 0) return 0;
+    const dim3 grid = grid_for(g.nx, g.ny, planes);
+    return (size_t)grid.x * grid.y * grid.z;
+}
+
+cudaError_t ks_residual_static(const LaunchCtx& cx_in, int km, bool pow2, const Geom& g, int zb, int ze, const PointK& k,
+                               const StencilOff& so, const double* v, const double* f, const double* aux, double* r,
+                               double** result_dev)
+{
+    constexpr int MAXDEV = 64;
+    static std::mutex mu;
+    static double* base_of[MAXDEV] = {};  // device address of the array, per device
+    if (ze <= zb || g.nx <= 0 || g.ny <= 0) return cudaErrorInvalidValue;
+    const size_t ctas = ks_residual_ctas(g, ze - zb);
+    if (ctas > (size_t)GS_STATIC_SCRATCH_MAX_CTAS) return cudaErrorInvalidValue;
+    int dev = -1;
+    if (cudaError_t e = cudaGetDevice(&dev)) return e;
+    if (dev < 0 || dev >= MAXDEV) return cudaErrorInvalidDevice;
+    double* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!base_of[dev]) {
+            void* ptr = nullptr;
+            if (cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_norm_scratch)) return e;
+            base_of[dev] = static_cast<double*>(ptr);
+        }
+        base = base_of[dev];
+    }
+    // the array keeps the last call's contents: result and ticket start from zero (the partial sums need not: every CTA
+    // writes its slot before the last one reads them)
+    if (cudaError_t e = cudaMemsetAsync(base + GS_STATIC_SCRATCH_MAX_CTAS, 0, 2 * sizeof(double), cx_in.stream)) return e;
+    LaunchCtx cx = cx_in;
+    cx.tune.pdl = 0;  // a plain launch behind the memset
+    cx.norm.partials = base;
+    cx.norm.result = base + GS_STATIC_SCRATCH_MAX_CTAS;
+    cx.norm.ticket = reinterpret_cast<unsigned int*>(base + GS_STATIC_SCRATCH_MAX_CTAS + 1);
+    cx.norm.cap = GS_STATIC_SCRATCH_MAX_CTAS;
+    ResidP p{g, k, {}, zb, v, f, aux, r, cx.norm};
+    fill_toff(g, so, p.toff);
+    dim3 grid = grid_for(g.nx, g.ny, ze - zb), block(BX, BY);
+    KM_DISPATCH(residual_simple, km, pow2, p);
+    if (result_dev) *result_dev = cx.norm.result;
     return done(cx);
 }
 

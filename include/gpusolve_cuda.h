@@ -140,6 +140,16 @@ int  gs_dump_field(gs_handle* h, int level, int field, const char* path);
 int  gs_smooth(gs_handle* h, int level, uint64_t iters);
 /* CpuSolver::compResidual(grid, level): r stored, returns sqrt(sum r^2)  :45-83 */
 int  gs_residual(gs_handle* h, int level, double* norm);
+/* gs_residual for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same inputs and outputs as
+ * gs_residual (r = f - A(v) stored on the level, *norm = sqrt(sum r^2)), but the call path allocates nothing: the scratch
+ * of the norm reduction is a static __device__ array inside the library (512 KB, held by every GPU that loads the library
+ * until the process exits) instead of memory from cudaMalloc.  Limits: the level may use at most 65536 reduction slots,
+ * ceil(nx/64) * ceil(ny/4) * nz <= 65536 (e.g. up to 255^3; larger levels return GS_EINVAL with a message), and must not
+ * be split into slabs (GS_EUNSUPPORTED).  All calls on a device share the one array, which keeps the last call's contents
+ * (the entry point clears what must start at zero): calls that overlap on the GPU — two handles on two streams of one
+ * device — race and must be serialised by the caller. */
+int  gs_residual_static(gs_handle* h, int level, double* norm);
 /* CpuSolver::restrict(level.src_field -> (level+1).dst_field)          :211-238 */
 int  gs_restrict(gs_handle* h, int level, int src_field, int dst_field);
 /* fused compResidual(level) ; restrict(r -> f_{level+1})            :93-98      */
