@@ -1,5 +1,5 @@
 #!/bin/bash
-# N-GPU bench lines only (each carries its own slab-vs-one-GPU parity record).  usage: bash tools/gpu_r02f.sh <tag> <ngpus> [cfg ...]
+# N-GPU bench lines only (each carries its own slab-vs-one-GPU parity record).  usage: bash tools/gpu_multi.sh <tag> <ngpus> [cfg ...]
 tag=$1; N=$2; shift 2
 out=gpurun_out; mkdir -p $out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517"
