@@ -127,6 +127,7 @@ struct gs_handle {
     size_t stage_count;   // doubles per half
     cudaStream_t io_stream;        // PCIe copies of field I/O; the pitch conversion runs on `stream`, one chunk behind
     cudaEvent_t io_copied[2], io_converted[2];
+    int opt_fuse_rv;      // FAS: R(v) -> restV, v computed by the fused residual+restriction pass (kernels_transfer.cu RV)
     int opt_fuse_pc;      // prolongation + correction folded into the first post-smoothing pass (kernels_fused.cu PC)
     int opt_p2p;          // slabs: ghost planes, coarse gather and norm through peer-mapped memory (kernels_comm.cu) instead of NCCL
     std::vector<long long> arena_offs;  // byte offset of every registered array in the arena (index level * GS_LEVEL_ARRAYS + slot; last = newtonF)
@@ -557,8 +558,11 @@ int do_restrict(gs_handle* h, int level, const double* fine, double* coarse, dou
 }
 
 // compResidual(level) ; restrict(r -> f_{level+1})     src/cpu/CpuSolver.cpp:93-98
-int do_restrict_residual(gs_handle* h, int level)
+// with_rv (FAS cycles, survey K5): the fused kernel also restricts v itself into restV and v of the coarse level in the same
+// pass; *rv_done tells the caller (do_fas_coarse_rhs) that this part of its work has been done
+int do_restrict_residual(gs_handle* h, int level, bool with_rv = false, bool* rv_done = nullptr)
 {
+    if (rv_done) *rv_done = false;
     Level& L = h->lev[level];
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_RESTRICT, level);
@@ -575,6 +579,18 @@ int do_restrict_residual(gs_handle* h, int level)
         int czb, cze;
         coarse_range(h, level, &czb, &cze);
         bool handled = false;
+        if (with_rv && rv_done && km == KM_NONLINEAR && h->opt_fuse_rv) {
+            CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, nullptr, C.f, &handled, C.restV, C.v));
+            if (handled) {
+                C.pre_valid = 0;
+                GS(finish_coarse(h, level, C.f));
+                GS(finish_coarse(h, level, C.restV));
+                GS(finish_coarse(h, level, C.v));
+                C.gv = 1;  // finish_coarse refreshed one ghost plane
+                *rv_done = true;
+                return GS_OK;
+            }
+        }
         CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, smoother_aux(h, level, km), C.f, &handled));
         if (handled) return finish_coarse(h, level, C.f);
     }
@@ -590,13 +606,15 @@ int do_restrict_residual(gs_handle* h, int level)
 }
 
 // FAS coarse right-hand side, src/cpu/CpuSolver.cpp:106-112
-int do_fas_coarse_rhs(gs_handle* h, int level)
+int do_fas_coarse_rhs(gs_handle* h, int level, bool rv_done = false)
 {
     Level& C = h->lev[level + 1];
     OpScope t(h, GS_OP_RESTRICT, level);
-    GS(need_v_halo(h, level, 1));
-    GS(do_restrict(h, level, h->lev[level].v, C.restV, C.v));
-    C.gv = 1;  // finish_coarse refreshed one ghost plane of both outputs
+    if (!rv_done) {  // else restV = v_{l+1} = R(v_l) came out of the fused residual+restriction pass
+        GS(need_v_halo(h, level, 1));
+        GS(do_restrict(h, level, h->lev[level].v, C.restV, C.v));
+        C.gv = 1;  // finish_coarse refreshed one ghost plane of both outputs
+    }
     CU(ks_fas_rhs(h->cx, C.pow2, C.g, C.ib, C.ie, C.k, h->so, C.restV, C.f, C.r));
     GS(exchange_halo(h, level + 1, C.f, 1));  // f changed on the owned planes only
     return GS_OK;
@@ -686,13 +704,14 @@ int enqueue_vcycle(gs_handle* h, bool host_norm = true)
     const int last = (int)h->lev.size() - 1;
     for (int i = 0; i < last; i++) {
         GS(do_smooth(h, i, h->p.pre));
-        GS(do_restrict_residual(h, i));
+        bool rv_done = false;
+        GS(do_restrict_residual(h, i, h->p.mode == GS_MODE_NONLINEAR, &rv_done));
         if (h->p.mode != GS_MODE_NONLINEAR) {
             if (h->opt_vzero) {
                 h->lev[i + 1].vzero_next = true;  // consumed by the do_smooth that follows
                 h->lev[i + 1].pre_valid = 0;
             } else GS(zero_field(h, h->lev[i + 1], h->lev[i + 1].v));
-        } else GS(do_fas_coarse_rhs(h, i));
+        } else GS(do_fas_coarse_rhs(h, i, rv_done));
     }
     GS(do_smooth(h, last, h->p.pre + h->p.post));
     if ((h->p.pre + h->p.post) & 1) {  // restore buffer parity on the (tiny) coarsest level
@@ -1201,6 +1220,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->arena_bytes = 0;
     h->opt_p2p = 1;
     if (const char* e = getenv("GPUSOLVE_P2P")) h->opt_p2p = atoi(e) != 0;
+    h->opt_fuse_rv = 1;
+    if (const char* e = getenv("GPUSOLVE_FUSE_RV")) h->opt_fuse_rv = atoi(e) != 0;
     h->opt_fuse_pc = 1;  // validated on the GPU (profiles/r02a_*): same bits, one pass per level and cycle fewer
     if (const char* e = getenv("GPUSOLVE_FUSE_PC")) h->opt_fuse_pc = std::max(0, std::min(2, atoi(e)));
     h->opt_device_stop = 1;
@@ -1958,6 +1979,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
     else if (n == "wave") h->cx.tune.wave = value != 0;
     else if (n == "device_stop") h->opt_device_stop = value != 0;
     else if (n == "p2p") h->opt_p2p = value != 0;
+    else if (n == "fuse_rv") h->opt_fuse_rv = value != 0;
     else if (n == "fuse_pc") h->opt_fuse_pc = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
     else if (n == "unit_taps") {  // 0: keep the six multiplies by -1.0 (A/B check; the bits do not change)
         h->opt_unit = value != 0;

@@ -168,4 +168,5 @@ cudaError_t kt_prolong_correct(const LaunchCtx& cx, const Geom& gf, const Geom& 
 cudaError_t kt_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int zcb, int zce, const double* fine, double* coarse,
                         double* coarse2, bool* handled);
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
-                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled);
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled,
+                              double* rv1 = nullptr, double* rv2 = nullptr);  // rv1/rv2 (mode 1): also R(v) -> both, within rounding

@@ -218,6 +218,9 @@ struct ResidRestrictP {
     const double* f;
     const double* aux;
     double* coarse;
+    // RV kernels (FAS, survey K5): the same pass also restricts v itself, R(v) -> rv1 and rv2 (restV and the coarse iterate)
+    double* rv1;
+    double* rv2;
 };
 
 // There is no producer warp: thread 0 issues the TMA loads right after the per-coarse-plane CTA barrier, which already
@@ -246,7 +249,13 @@ struct RRCfg {
 
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 
-template <int KM, int AR, int CX, int CY, int NSTAGE>
+// RV: full weighting of v itself in the same pass (src/cpu/CpuSolver.cpp:106-107, the two restrict(v) calls of the FAS
+// coarse right-hand side): the nine v values a coarse point needs on a fine plane are the thread's own 2 x 2, the east and
+// north neighbours it loads for the residual anyway, and one corner.  The plane sums are combined as
+// 0.125 (0.5 P(2Z-1) + P(2Z) + 0.5 P(2Z+1)): the same 27 exact products as the reference's running sum, added plane by
+// plane instead of z-innermost, i.e. equal to it within rounding (~1e-16), not bit for bit — used only inside the V-cycle
+// of the exp() mode, whose tolerance is 1e-12; the operator entry points keep restrict_zmarch.
+template <int KM, int AR, int CX, int CY, int NSTAGE, bool RV = false>
 __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
     resid_restrict_tma(const __grid_constant__ CUtensorMap map_v, ResidRestrictP p)
 {
@@ -315,6 +324,7 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
             a2 = ld2 ? __ldg(reinterpret_cast<const double2*>(p.aux + c0 + pitch)) : zero2;
         }
         double rB11 = 0, rB21 = 0, rB12 = 0, rB22 = 0, r11 = 0, r21 = 0, r12 = 0, r22 = 0;
+        double pv = 0, pvA = 0, pvB = 0;  // RV: weighted nine-point sums of v on the last plane, on planes 2j and 2j+1
 
         // one residual plane t (v centre plane q = t+1): own four points, stored to slot t
         auto do_plane = [&](int t) {
@@ -346,6 +356,19 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
             const double2 U1 = lds2(vu + o11), U2 = lds2(vu + o11 + VW);
             const double2 S = lds2(vb + o11 - VW), N = lds2(vb + o11 + 2 * VW);
             const double W1 = vb[o11 - 1], W2 = vb[o11 + VW - 1], E1 = vb[o11 + 2], E2 = vb[o11 + VW + 2];
+            if (RV) {
+                const double NE = vb[o11 + 2 * VW + 2];  // (2X+1, 2Y+1)
+                double s = 0.25 * C1.x;
+                s += 0.5 * C2.x;
+                s += 0.25 * N.x;
+                s += 0.5 * C1.y;
+                s += C2.y;
+                s += 0.5 * N.y;
+                s += 0.25 * E1;
+                s += 0.5 * E2;
+                s += 0.25 * NE;
+                pv = s;
+            }
             const bool mz = zgA + t <= p.gf.nz;
             double den;
             r11 = canon_residual<KM, AR>(C1.x, C1.y, W1, C2.x, S.x, U1.x, D1.x, f1.x, a1.x, p.k, den);
@@ -371,11 +394,13 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
     acc += (0.125 * WI * WJ * 1.0) * (B);      \
     acc += (0.125 * WI * WJ * 0.5) * (C);
         do_plane(0);
+        pvA = pv;
         const bool live = X <= p.gc.nx && Y <= p.gc.ny;
         i64 cc = gs_idx(p.gc, min(X, p.gc.nx), min(Y, p.gc.ny), zc0);
         for (int j = 0; j < nzc; j++) {
             do_plane(2 * j + 1);
             rB11 = r11; rB21 = r21; rB12 = r12; rB22 = r22;
+            pvB = pv;
             do_plane(2 * j + 2);
             consumer_sync<Cfg::NCONS>();
             refill(j);
@@ -397,6 +422,14 @@ __global__ void __launch_bounds__(RRCfg<CX, CY, NSTAGE>::THREADS, 2)
             TERM(0.5, 1.0, sA[oO + Cfg::ROW_O + 1], sB[oO + Cfg::ROW_O + 1], sC[oO + Cfg::ROW_O + 1])
             TERM(0.5, 0.5, sA[oO + 2 * Cfg::ROW_O + 1], sB[oO + 2 * Cfg::ROW_O + 1], sC[oO + 2 * Cfg::ROW_O + 1])
             if (live) p.coarse[cc] = acc;
+            if (RV) {
+                const double rv = 0.125 * ((0.5 * pvA + pvB) + 0.5 * pv);
+                if (live) {
+                    p.rv1[cc] = rv;
+                    p.rv2[cc] = rv;
+                }
+                pvA = pv;
+            }
             cc += p.gc.plane;
         }
 #undef TERM
@@ -500,17 +533,17 @@ cudaError_t kt_restrict(const LaunchCtx& cx, const Geom& gf, const Geom& gc, int
 
 namespace {
 
-template <int KM, int AR, int CX, int CY, int NSTAGE>
+template <int KM, int AR, int CX, int CY, int NSTAGE, bool RV = false>
 cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 {
     using Cfg = RRCfg<CX, CY, NSTAGE>;
     static DevOnce once;
     int occ = 1;
     cudaError_t pe = gs_dev_once(once, &occ, [](int* o) {
-        cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, AR, CX, CY, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(resid_restrict_tma<KM, AR, CX, CY, NSTAGE, RV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, resid_restrict_tma<KM, AR, CX, CY, NSTAGE>, Cfg::THREADS, Cfg::SMEM);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(o, resid_restrict_tma<KM, AR, CX, CY, NSTAGE, RV>, Cfg::THREADS, Cfg::SMEM);
         return e;
     });
     if (pe != cudaSuccess) return pe;
@@ -522,7 +555,7 @@ cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
     if (cx.tune.wave) p.zchunk = gs_pick_zchunk_waves(cx, tx * ty, p.zce - p.zcb, occ, 3, 4, 64, false);
     else p.zchunk = gs_pick_zchunk(cx, tx * ty, p.zce - p.zcb, 32);
     dim3 grid(tx, ty, (p.zce - p.zcb + p.zchunk - 1) / p.zchunk);
-    resid_restrict_tma<KM, AR, CX, CY, NSTAGE><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, p);
+    resid_restrict_tma<KM, AR, CX, CY, NSTAGE, RV><<<grid, Cfg::THREADS, Cfg::SMEM, cx.stream>>>(mv, p);
     *handled = true;
     return cudaGetLastError();
 }
@@ -530,6 +563,13 @@ cudaError_t launch_rr(const LaunchCtx& cx, ResidRestrictP p, bool* handled)
 template <int KM, int AR>
 cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, bool* handled)
 {
+    if constexpr (KM == KM_NONLINEAR) {  // FAS: R(v) in the same pass (the six-stage ring only)
+        if (p.rv1 || !p.v) {
+            cudaError_t e = launch_rr<KM, AR, 32, 8, 6, true>(cx, p, handled);
+            if (e != cudaSuccess || p.v) return e;
+        }
+    }
+    if (p.rv1) return cudaSuccess;  // not handled
     if (cfg == 1) return launch_rr<KM, AR, 32, 8, 6>(cx, p, handled);
     return launch_rr<KM, AR, 32, 8, 5>(cx, p, handled);
 }
@@ -539,7 +579,8 @@ cudaError_t dispatch_rr(const LaunchCtx& cx, const ResidRestrictP& p, int cfg, b
 // f_{l+1}(coarse interior planes [zcb, zce)) = R(f_l - A_l v_l); the fine level must hold v planes
 // 2*Zc-2 .. 2*Zc+2 of every coarse plane Zc it is asked for
 cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& gf, const Geom& gc, int zcb, int zce,
-                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled)
+                              const PointK& k, const double* v, const double* f, const double* aux, double* coarse, bool* handled,
+                              double* rv1, double* rv2)
 {
     *handled = false;
     int cfg = 0;
@@ -548,7 +589,7 @@ cudaError_t kt_resid_restrict(const LaunchCtx& cx, int km, int ar, const Geom& g
         if (gc.nx < 24 || gc.ny < 8 || zce - zcb < 4) return cudaSuccess;  // small levels: unfused simple kernels
         cfg = cx.tune.rr_variant;
     }
-    ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse};
+    ResidRestrictP p{gf, gc, k, zcb, zce, 0, v, f, aux, coarse, rv1, rv2};
     cudaError_t e = cudaSuccess;
     for (int c = v ? cfg : 0; c <= (v ? cfg : 1) && e == cudaSuccess; c++) {
 #define CALL(KMV) AR_SWITCH(ar, e = (dispatch_rr<KMV, ARV>(cx, p, c, handled)))

@@ -31,6 +31,7 @@ int  gs_time_halo_exchange(gs_handle* h, int level, int depth, int reps, double*
  *   "unit_taps", "rcp_div", "wave", "vzero" = 0/1 arithmetic / scheduling shortcuts (A/B switches, default 1)
  *   "fuse_pc" = 0/1/2 prolongation + correction folded into the first post-smoothing pass (default 1: linear mode only; 2: every mode)
  *   "device_stop" = 0/1 inner Newton solves as one conditional CUDA graph with the stopping test on the device
+ *   "fuse_rv" = 0/1 FAS cycles: R(v) -> restV, v formed by the fused residual+restriction pass (default 1; equal within rounding)
  *   "pdl" = 0/1 small-level kernels launched with programmatic stream serialization (default 1)
  *   "s2_ty" = 0/10/12 tile height of the two-sweep kernel (0: per mode)
  *   "p2p" = 0/1 slabs: ghost planes pushed through peer-mapped memory instead of NCCL send/recv */

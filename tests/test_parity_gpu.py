@@ -373,3 +373,42 @@ def test_prolongation_folded_into_the_post_smoother_keeps_the_bits(gs, mode, n, 
             assert norms == rn
             assert b.launches - l0 < per_run, "no prolongation launch was folded away"
         b.close()
+
+
+@pytest.mark.parametrize("n,pre,post", [(127, 2, 2), (191, 2, 2), ((121, 64, 70), 4, 2), (120, 3, 3), (511, 2, 2)])
+def test_fas_restriction_of_v_folded_into_the_residual_restriction(gs, n, pre, post):
+    """fuse_rv (survey K5, src/cpu/CpuSolver.cpp:106-107): in FAS cycles the fused residual+restriction pass also forms
+    restV = v_{l+1} = R(v_l) — the same 27 exact products as the reference's running sum, added plane by plane, so equal
+    to the separate restriction within rounding (1e-12 is the tolerance of the exp() mode), one fine-grid launch per level
+    fewer, and deterministic from run to run"""
+    kw = dict(n=n, mode=1, pre=pre, post=post, maxiter=1, tol=1e-30)
+    ref = CudaBackend(gs, kernels=1, graph=0, **kw)
+    ref.set_option("fuse_rv", 0)
+    v0 = seeded_field(ref.shape(0), 21)
+
+    def run(b):
+        b.set(0, V, v0)
+        norms = [b.vcycle() for _ in range(3)]
+        return norms, b.get(0, V), b.get(1, RESTV)
+
+    rn, rv, rrest = run(ref)
+    l0 = ref.launches
+    run(ref)
+    per_run = ref.launches - l0
+    ref.close()
+    for graph in (0, 1):
+        b = CudaBackend(gs, kernels=1, graph=graph, **kw)
+        b.set_option("fuse_rv", 1)
+        seen = set()
+        for rep in range(2):
+            l0 = b.launches
+            norms, v, rest = run(b)
+            assert rel_err(v, rv) <= FIELD_TOL, f"graph {graph} rep {rep}: v rel err {rel_err(v, rv):.3e}"
+            assert rel_err(rest, rrest) <= FIELD_TOL, f"graph {graph} rep {rep}: restV rel err {rel_err(rest, rrest):.3e}"
+            for x, y in zip(norms, rn):
+                check_norm(f"graph {graph} rep {rep} norm", x, y)
+            if graph == 0:
+                assert b.launches - l0 < per_run, "no restriction launch was folded away"
+            seen.add(digest(v))
+        assert len(seen) == 1, "fused path is not deterministic"
+        b.close()
