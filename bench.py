@@ -405,6 +405,9 @@ def slab_parity(job, n=255, cycles=2):
             ok, nerr = True, 0.0
             if job.rank == 0:
                 one = job.solver(n, mode=mode, pre=pre, post=pre, slab=False)
+                # FAS: a one-GPU handle folds R(v) into the fused residual+restriction pass (equal to the separate restriction
+                # within rounding, not bit for bit); slab handles never do, so the bitwise comparison is made with it off
+                one.set_option("fuse_rv", 0)
                 ref = [step(one) for _ in range(cycles)]
                 want = [one.get(l, field if (mode == 2 and l == 0) else gs.V) for l in (0, 1)]
                 ok = all(bool(np.array_equal(a, b)) for a, b in zip(got, want))

@@ -579,7 +579,11 @@ int do_restrict_residual(gs_handle* h, int level, bool with_rv = false, bool* rv
         int czb, cze;
         coarse_range(h, level, &czb, &cze);
         bool handled = false;
-        if (with_rv && rv_done && km == KM_NONLINEAR && h->opt_fuse_rv) {
+        // One-GPU handles only: on slabs a rank with fewer than four coarse planes has to take the separate (bit-exact)
+        // restriction, and the two orders of summation differ in the last bit — which would cost the property that slab
+        // fields equal the one-GPU fields bit for bit (seen at world 8, n = 255).  Slab handles therefore always form R(v)
+        // with the separate restriction; compare them with a one-GPU handle that has fuse_rv = 0.
+        if (with_rv && rv_done && km == KM_NONLINEAR && h->opt_fuse_rv && h->world == 1) {
             CU(kt_resid_restrict(h->cx, km, L.ar, L.g, C.g, czb, cze, L.k, L.v, L.f, nullptr, C.f, &handled, C.restV, C.v));
             if (handled) {
                 C.pre_valid = 0;

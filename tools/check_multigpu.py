@@ -46,6 +46,7 @@ def main():
     got1 = slab.get(1, field if args.mode == 2 else gs.V)
     if rank == 0:
         one = gs.GpuSolve(p, device=local)
+        one.set_option("fuse_rv", 0)   # slab handles form R(v) with the separate, bit-exact restriction (gs_api.cu do_restrict_residual)
         ref = []
         if args.mode == 2:
             for _ in range(args.cycles):
