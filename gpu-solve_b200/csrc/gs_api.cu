@@ -672,6 +672,9 @@ int try_prolong_smooth2(gs_handle* h, int level, bool* done)
     // cycle 5.61 against 5.46 ms, V(2,2) 4.04 against 3.82 (profiles/r02k_levels_mode1_fuse_pc.txt, r02ad_fuse_pc_mode2.txt).
     // fuse_pc = 2 forces it in every mode for A/B and for the parity test.
     if (km != KM_LINEAR && h->opt_fuse_pc < 2) return GS_OK;
+    // ... and only the large levels: at 255^3 and below the fused pass (latency-bound, one wave or two of CTAs) is no faster
+    // than the two it replaces (0.206 against 0.143 + 0.051 ms for the level-1 smoother launches of a 513^3 cycle)
+    if (F.g.nx < h->cx.tune.pc_min_n && h->opt_fuse_pc < 2) return GS_OK;
     if (F.g.nx < h->cx.tune.fuse2_min_n || F.g.ny < 16 || F.ie - F.ib < 16 || !slab_planes_ok(h, level, 16))
         return GS_OK;  // kx_smooth2 would decline (on this rank or on another)
     if (km == KM_NEWTON_COEF) GS(ensure_coef(h, level));
@@ -1385,6 +1388,8 @@ int create_impl(const gs_params* p, int device, int rank, int world, const void*
     h->cx.tune.rr_variant = 1;  // six-stage ring
     h->cx.tune.fuse2 = 1;
     h->cx.tune.fuse2_min_n = 96;
+    h->cx.tune.pc_min_n = 384;
+    if (const char* ev = getenv("GPUSOLVE_PC_MIN_N")) h->cx.tune.pc_min_n = atoi(ev);
     h->cx.tune.pdl = 1;
     if (const char* ev = getenv("GPUSOLVE_PDL")) h->cx.tune.pdl = atoi(ev) != 0;
     h->cx.tune.s2_ty = 0;
@@ -1993,6 +1998,7 @@ int gs_set_option(gs_handle* h, const char* name, int64_t value)
         h->cx.tune.fuse2 = (int)std::max<int64_t>(0, std::min<int64_t>(2, value));
         h->lev[0].pre_valid = 0;
     } else if (n == "fuse2_min_n") h->cx.tune.fuse2_min_n = (int)value;
+    else if (n == "pc_min_n") h->cx.tune.pc_min_n = (int)value;
     else if (n == "pdl") h->cx.tune.pdl = value != 0;
     else if (n == "s2_ty") h->cx.tune.s2_ty = (int)value;
     else if (n == "zchunk2") h->cx.tune.zchunk2 = (int)std::max<int64_t>(8, value);

@@ -67,6 +67,7 @@ struct Tune {
     int rr_variant;      // fused residual+restriction kernel: 0 = five-stage ring, 1 = six-stage (default)
     int fuse2;           // two sweeps per pass (kernels_fused.cu): 0 off, 1 = five-stage ring, 2 = four-stage
     int fuse2_min_n;     // levels with fewer interior points per axis sweep one at a time
+    int pc_min_n;        // levels with fewer interior points per axis keep prolongation + correction as its own pass
     int pdl;             // one-thread-per-point kernels are launched with programmatic stream serialization (kernels_simple.cu)
     int s2_ty;           // tile height of the two-sweep kernel: 0 = per mode (12 linear, 10 otherwise), 10 / 12 forced (A/B)
     int zchunk2;         // planes per CTA of the two-sweep kernel

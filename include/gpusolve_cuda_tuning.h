@@ -29,7 +29,7 @@ int  gs_time_halo_exchange(gs_handle* h, int level, int depth, int reps, double*
  *   "fuse2" = 0 one Jacobi sweep per pass, 1 two sweeps per pass (kernels_fused.cu), "fuse2_min_n", "zchunk2"
  *   "fuse_norm" = 0/1 produce the next pre-smoothing sweeps together with the V-cycle's final residual norm
  *   "unit_taps", "rcp_div", "wave", "vzero" = 0/1 arithmetic / scheduling shortcuts (A/B switches, default 1)
- *   "fuse_pc" = 0/1/2 prolongation + correction folded into the first post-smoothing pass (default 1: linear mode only; 2: every mode)
+ *   "fuse_pc" = 0/1/2 prolongation + correction folded into the first post-smoothing pass (default 1: linear mode, levels of >= "pc_min_n" = 384 points per axis; 2: every mode and level)
  *   "device_stop" = 0/1 inner Newton solves as one conditional CUDA graph with the stopping test on the device
  *   "fuse_rv" = 0/1 FAS cycles: R(v) -> restV, v formed by the fused residual+restriction pass (default 1; equal within rounding)
  *   "pdl" = 0/1 small-level kernels launched with programmatic stream serialization (default 1)
